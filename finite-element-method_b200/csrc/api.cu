@@ -1,0 +1,435 @@
+// api.cu -- the extern "C" surface of include/femb200.h: object lifetime, field
+// marshalling, explicit path.  (The implicit solve lives in api_solve.cu.)
+#include <cmath>
+#include <cstring>
+
+#include "object.h"
+
+using namespace femb;
+
+namespace femb {
+thread_local std::string g_last_error;
+
+int fail(const std::exception& ex) {
+  g_last_error = ex.what();
+  if (dynamic_cast<const ArgError*>(&ex)) return FEMB_E_ARG;
+  if (dynamic_cast<const StateError*>(&ex)) return FEMB_E_STATE;
+  if (dynamic_cast<const LimitError*>(&ex)) return FEMB_E_LIMIT;
+  return FEMB_E_CUDA;
+}
+}  // namespace femb
+
+#define FEMB_TRY try {
+#define FEMB_CATCH                   \
+  }                                  \
+  catch (const std::exception& ex) { \
+    return femb::fail(ex);           \
+  }                                  \
+  return FEMB_OK;
+
+void femb_object::ensure_stage(size_t floats) {
+  if (floats <= stage_floats) return;
+  // grow-only; the old buffer stays in `allocs` and is freed with the object
+  d_stage = alloc<float>(floats, false);
+  stage_floats = floats;
+}
+
+KinArgs femb_object::kin_args(float dt, const float* g_dir) const {
+  if (!g_dir) throw ArgError("g_dir is NULL");
+  KinArgs k{};
+  k.dt = dt;
+  for (int i = 0; i < 3; ++i) k.g98[i] = i < dim ? 9.8f * g_dir[i] : 0.f;
+  k.damp = expf(-dt * mat.damping);  // ti.exp(-dt * damping), kinematic.py:23
+  k.blocks.data = d_blocks;
+  k.blocks.count = n_blocks;
+  return k;
+}
+
+static const int kMaxSmem = 227 * 1024;
+
+static int tile_smem_bytes(const Tiling& t) {
+  const int stride = (t.max_tile_elems + 31) / 32 * 32;
+  return t.max_lv * (int)sizeof(float4) + t.dim * t.dim * stride * (int)sizeof(float);
+}
+
+extern "C" {
+
+const char* femb_last_error(void) { return g_last_error.c_str(); }
+uint64_t femb_launch_count(void) { return launch_count(); }
+const char* femb_version(void) { return "femb200 0.1 (sm_100a)"; }
+
+int femb_object_create(const femb_desc* d, femb_object** out) {
+  femb_object* o = nullptr;
+  try {
+    if (!d || !out) throw ArgError("femb_object_create: NULL argument");
+    *out = nullptr;
+    if (d->dim != 2 && d->dim != 3) throw ArgError("dim must be 2 or 3");
+    if (d->n_vert <= 0 || d->n_elem <= 0 || !d->verts || !d->elems) throw ArgError("empty mesh");
+    if (!(d->rho > 0.f)) throw ArgError("rho must be positive");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+      cudaGetLastError();
+      throw CudaError("no CUDA device: libfemb200 has no CPU fallback");
+    }
+    o = new femb_object();
+    if (d->device >= 0) FEMB_CUDA(cudaSetDevice(d->device));
+    FEMB_CUDA(cudaGetDevice(&o->device));
+    o->dim = d->dim; o->n_vert = d->n_vert; o->n_elem = d->n_elem;
+    o->implicit = d->implicit != 0;
+    o->mat = Material{d->mu, d->lambda, d->rho, d->damping};
+    const int dim = d->dim;
+
+    // pos = raw + center in fp32                       (object.py:341)
+    std::vector<float> pos((size_t)d->n_vert * dim);
+    for (int v = 0; v < d->n_vert; ++v)
+      for (int k = 0; k < dim; ++k) pos[(size_t)v * dim + k] = d->verts[(size_t)v * dim + k] + d->center[k];
+
+    int T = d->tile_elems > 0 ? d->tile_elems : (dim == 3 ? 2304 : 2048);
+    for (;;) {
+      const std::string err = build_tiling(dim, d->n_vert, d->n_elem, pos.data(), d->elems, T, o->til);
+      if (!err.empty()) throw ArgError(err);
+      if (tile_smem_bytes(o->til) <= kMaxSmem) break;
+      if (T <= 64) throw LimitError("tiling does not fit shared memory even with 64-element tiles");
+      T /= 2;  // irregular mesh with very many vertices per tile: shrink the tiles
+    }
+    const Tiling& t = o->til;
+
+    FEMB_CUDA(cudaStreamCreateWithFlags(&o->stream, cudaStreamNonBlocking));
+    o->own_stream = true;
+    cudaDeviceProp prop{};
+    FEMB_CUDA(cudaGetDeviceProperties(&prop, o->device));
+    o->cfg = LaunchCfg{o->stream, 256, tile_smem_bytes(t), prop.multiProcessorCount, o->device};
+
+    auto upload = [&](auto*& dst, const auto& vec) {
+      using T_ = typename std::remove_reference<decltype(vec)>::type::value_type;
+      dst = o->alloc<T_>(vec.size(), false);
+      if (!vec.empty())
+        FEMB_CUDA(cudaMemcpyAsync(dst, vec.data(), vec.size() * sizeof(T_), cudaMemcpyHostToDevice, o->stream));
+    };
+    TileDesc* d_tiles; LocalVert* d_lv; uint16_t* d_jds; uint32_t* d_rounds; int32_t* d_bptr;
+    upload(d_tiles, t.tiles);
+    upload(d_lv, t.lv);
+    upload(d_jds, t.jds);
+    upload(d_rounds, t.rounds);
+    upload(d_bptr, t.bptr);
+    upload(o->d_lidx, t.lidx);
+    upload(o->d_new_of_old, t.new_of_old);
+    upload(o->d_slot_of_elem, t.slot_of_elem);
+    o->dtl = DevTiling{d_tiles, d_lv, d_jds, d_rounds, d_bptr, t.n_tiles, t.n_interior, t.n_boundary, t.n_vert,
+                       t.n_slots, (t.max_tile_elems + 31) / 32 * 32, t.max_lv};
+
+    const size_t ns = (size_t)t.n_slots, nv = (size_t)t.n_vert;
+    o->e.p0 = o->alloc<float4>(ns);
+    o->e.p1 = o->alloc<float4>(ns);
+    o->e.p2 = dim == 3 ? o->alloc<float4>(ns) : nullptr;
+    o->vs.pos = o->alloc<float4>(nv);
+    o->vs.vel = o->alloc<float4>(nv);
+    o->vs.force = o->alloc<float4>(nv);
+    o->vs.grad = o->alloc<float4>(nv);
+    o->vs.partial = o->alloc<float4>((size_t)t.n_partials);
+    o->ref_pos = o->alloc<float4>(nv);
+    o->d_phi = o->alloc<float>(ns);
+    o->red_slots = reduce_slots(o->dtl, o->cfg);
+    o->d_red = o->alloc<double>((size_t)o->red_slots);
+    o->d_U = o->alloc<double>(1);
+    if (o->implicit) {
+      o->h.p0 = o->alloc<float4>(ns);
+      o->h.p1 = o->alloc<float4>(ns);
+      o->h.p2 = dim == 3 ? o->alloc<float4>(ns) : nullptr;
+      o->vs.vel_g = o->alloc<float4>(nv);
+      float4** vecs[] = {&o->iv.b, &o->iv.x, &o->iv.past_x, &o->iv.d, &o->iv.r,
+                         &o->iv.q, &o->iv.atb, &o->iv.tmp, &o->iv.diag};
+      for (float4** p : vecs) *p = o->alloc<float4>(nv);
+      o->d_sc = o->alloc<SolveScalars>(1);
+      FEMB_CUDA(cudaMallocHost(&o->h_sc, sizeof(SolveScalars)));
+    }
+
+    // positions in, then Dm^-1 / volume / mass on the device (object.py:71-73)
+    o->ensure_stage(nv * 3);
+    FEMB_CUDA(cudaMemcpyAsync(o->d_stage, pos.data(), pos.size() * sizeof(float), cudaMemcpyHostToDevice, o->stream));
+    launch_unpack_vertex(o->cfg, dim, t.n_vert, o->d_new_of_old, o->d_stage, 0, dim, o->vs.pos);
+    launch_setup(dim, o->cfg, o->dtl, o->e, o->d_lidx, o->vs, o->mat);
+    FEMB_CUDA(cudaMemcpyAsync(o->ref_pos, o->vs.pos, nv * sizeof(float4), cudaMemcpyDeviceToDevice, o->stream));
+    FEMB_CUDA(cudaStreamSynchronize(o->stream));
+    *out = o;
+  } catch (const std::exception& ex) {
+    if (o) femb_object_destroy(o);
+    return femb::fail(ex);
+  }
+  return FEMB_OK;
+}
+
+int femb_object_destroy(femb_object* o) {
+  if (!o) return FEMB_OK;
+  cudaSetDevice(o->device);
+  if (o->stream) cudaStreamSynchronize(o->stream);
+  if (o->graph.exec) cudaGraphExecDestroy(o->graph.exec);
+  for (void* p : o->allocs) cudaFree(p);
+  if (o->h_sc) cudaFreeHost(o->h_sc);
+  if (o->own_stream && o->stream) cudaStreamDestroy(o->stream);
+  cudaGetLastError();
+  delete o;
+  return FEMB_OK;
+}
+
+static void fill_info(const Tiling& t, femb_info* i) {
+  std::memset(i, 0, sizeof(*i));
+  i->dim = t.dim; i->n_vert = t.n_vert; i->n_elem = t.n_elem;
+  i->n_tiles = t.n_tiles; i->tile_elems = t.T; i->max_tile_verts = t.max_lv; i->max_rounds = t.max_rounds;
+  i->n_interior = t.n_interior; i->n_boundary = t.n_boundary; i->n_partials = t.n_partials;
+  i->smem_bytes = tile_smem_bytes(t);
+  i->block_threads = 256;
+}
+
+int femb_object_info(const femb_object* o, femb_info* out) {
+  FEMB_TRY
+  if (!o || !out) throw ArgError("femb_object_info: NULL argument");
+  fill_info(o->til, out);
+  out->device_bytes = o->device_bytes;
+  FEMB_CATCH
+}
+
+int femb_set_stream(femb_object* o, void* s) {
+  FEMB_TRY
+  if (!o) throw ArgError("NULL object");
+  FEMB_CUDA(cudaStreamSynchronize(o->stream));
+  if (o->own_stream) cudaStreamDestroy(o->stream);
+  o->own_stream = false;
+  o->stream = static_cast<cudaStream_t>(s);
+  o->cfg.stream = o->stream;
+  if (o->graph.exec) { cudaGraphExecDestroy(o->graph.exec); o->graph = StepGraph(); }
+  FEMB_CATCH
+}
+
+int femb_blocks_set(femb_object* o, int32_t n, const float* centers, const float* radii) {
+  FEMB_TRY
+  if (!o || n < 0 || (n > 0 && (!centers || !radii))) throw ArgError("femb_blocks_set: bad argument");
+  std::vector<float4> b((size_t)n);
+  for (int i = 0; i < n; ++i) {
+    b[i].x = centers[(size_t)i * o->dim + 0];
+    b[i].y = centers[(size_t)i * o->dim + 1];
+    b[i].z = o->dim == 3 ? centers[(size_t)i * 3 + 2] : 0.f;
+    b[i].w = radii[i];
+  }
+  FEMB_CUDA(cudaStreamSynchronize(o->stream));
+  o->d_blocks = n ? o->alloc<float4>((size_t)n, false) : nullptr;
+  if (n) FEMB_CUDA(cudaMemcpyAsync(o->d_blocks, b.data(), b.size() * sizeof(float4), cudaMemcpyHostToDevice, o->stream));
+  FEMB_CUDA(cudaStreamSynchronize(o->stream));
+  o->n_blocks = n;
+  o->blocks_version++;
+  FEMB_CATCH
+}
+
+int femb_explicit_grad(femb_object* o) {
+  FEMB_TRY
+  if (!o) throw ArgError("NULL object");
+  FEMB_CUDA(cudaSetDevice(o->device));
+  launch_explicit(o->dim, EX_GRAD, o->cfg, o->dtl, o->e, o->vs, o->mat, KinArgs{}, nullptr, nullptr);
+  FEMB_CATCH
+}
+
+int femb_energy_grad(femb_object* o, float* U_out) {
+  FEMB_TRY
+  if (!o) throw ArgError("NULL object");
+  FEMB_CUDA(cudaSetDevice(o->device));
+  launch_explicit(o->dim, EX_ENERGY, o->cfg, o->dtl, o->e, o->vs, o->mat, KinArgs{}, o->d_phi, o->d_red);
+  const int nbb = (o->dtl.n_boundary + 255) / 256;
+  launch_reduce_final(o->cfg, o->dtl.n_tiles + nbb, o->d_red, o->d_U);
+  if (U_out) return femb_get_energy(o, U_out);
+  FEMB_CATCH
+}
+
+int femb_get_energy(femb_object* o, float* U_out) {
+  FEMB_TRY
+  if (!o || !U_out) throw ArgError("NULL argument");
+  double u = 0.0;
+  FEMB_CUDA(cudaMemcpyAsync(&u, o->d_U, sizeof(double), cudaMemcpyDeviceToHost, o->stream));
+  FEMB_CUDA(cudaStreamSynchronize(o->stream));
+  *U_out = (float)u;
+  FEMB_CATCH
+}
+
+int femb_kinematic(femb_object* o, float dt, const float* g_dir, int32_t use_grad) {
+  FEMB_TRY
+  if (!o) throw ArgError("NULL object");
+  FEMB_CUDA(cudaSetDevice(o->device));
+  launch_kinematic(o->dim, o->cfg, o->n_vert, o->vs, o->kin_args(dt, g_dir), use_grad);
+  FEMB_CATCH
+}
+
+int femb_explicit_step(femb_object* o, float dt, const float* g_dir, int32_t n_steps) {
+  FEMB_TRY
+  if (!o || n_steps < 0) throw ArgError("femb_explicit_step: bad argument");
+  FEMB_CUDA(cudaSetDevice(o->device));
+  const KinArgs kin = o->kin_args(dt, g_dir);
+  auto run = [&]() {
+    for (int s = 0; s < n_steps; ++s)
+      launch_explicit(o->dim, EX_STEP, o->cfg, o->dtl, o->e, o->vs, o->mat, kin, nullptr, nullptr);
+  };
+  if (n_steps < 4) {
+    run();
+  } else {
+    StepGraph& g = o->graph;
+    const bool hit = g.exec && g.n_steps == n_steps && g.dt == dt && g.damp == kin.damp &&
+                     g.blocks_version == o->blocks_version && std::memcmp(g.g, kin.g98, sizeof(g.g)) == 0;
+    if (!hit) {
+      if (g.exec) { cudaGraphExecDestroy(g.exec); g = StepGraph(); }
+      // warm the function attributes outside the capture
+      cudaGraph_t graph = nullptr;
+      const uint64_t before = launch_count();
+      FEMB_CUDA(cudaStreamBeginCapture(o->stream, cudaStreamCaptureModeThreadLocal));
+      try {
+        run();
+      } catch (...) {
+        cudaStreamEndCapture(o->stream, &graph);
+        if (graph) cudaGraphDestroy(graph);
+        throw;
+      }
+      FEMB_CUDA(cudaStreamEndCapture(o->stream, &graph));
+      const cudaError_t ie = cudaGraphInstantiate(&g.exec, graph, 0);
+      cudaGraphDestroy(graph);
+      cuda_check(ie, "cudaGraphInstantiate");
+      g.launches = launch_count() - before;
+      g.n_steps = n_steps; g.dt = dt; g.damp = kin.damp; g.blocks_version = o->blocks_version;
+      std::memcpy(g.g, kin.g98, sizeof(g.g));
+    } else {
+      for (uint64_t i = 0; i < g.launches; ++i) note_launch("graph", o->stream);
+    }
+    FEMB_CUDA(cudaGraphLaunch(g.exec, o->stream));
+  }
+  FEMB_CATCH
+}
+
+int femb_advect_implicit(femb_object* o, float dt, const float* g_dir) {
+  FEMB_TRY
+  if (!o) throw ArgError("NULL object");
+  if (!o->implicit) throw StateError("object was created without implicit buffers");
+  FEMB_CUDA(cudaSetDevice(o->device));
+  launch_advect_implicit(o->dim, o->cfg, o->n_vert, o->vs, o->kin_args(dt, g_dir));
+  FEMB_CATCH
+}
+
+int femb_sync(femb_object* o) {
+  FEMB_TRY
+  if (!o) throw ArgError("NULL object");
+  FEMB_CUDA(cudaStreamSynchronize(o->stream));
+  FEMB_CATCH
+}
+
+// ---- field access ---------------------------------------------------------
+struct FieldRef {
+  float4* vec = nullptr;   // vertex field
+  int comp0 = 0, ncomp = 0;
+  int elem_what = -1;      // element field selector for k_pack_elem
+  size_t count = 0;        // floats on the host side
+};
+
+static FieldRef resolve(femb_object* o, int field) {
+  FieldRef r;
+  const size_t nv = (size_t)o->n_vert, ne = (size_t)o->n_elem, d = (size_t)o->dim;
+  auto vec = [&](float4* p) { r.vec = p; r.comp0 = 0; r.ncomp = o->dim; r.count = nv * d; };
+  auto need_implicit = [&]() { if (!o->implicit) throw StateError("field needs an implicit object"); };
+  switch (field) {
+    case FEMB_F_POS: vec(o->vs.pos); break;
+    case FEMB_F_VEL: vec(o->vs.vel); break;
+    case FEMB_F_VEL_G: need_implicit(); vec(o->vs.vel_g); break;
+    case FEMB_F_FORCE: vec(o->vs.force); break;
+    case FEMB_F_GRAD: vec(o->vs.grad); break;
+    case FEMB_F_MASS: r.vec = o->vs.pos; r.comp0 = 3; r.ncomp = 1; r.count = nv; break;
+    case FEMB_F_REF_POS: vec(o->ref_pos); break;
+    case FEMB_F_VEC_B: need_implicit(); vec(o->iv.b); break;
+    case FEMB_F_VEC_X: need_implicit(); vec(o->iv.x); break;
+    case FEMB_F_PAST_X: need_implicit(); vec(o->iv.past_x); break;
+    case FEMB_F_DIAG_A: need_implicit(); vec(o->iv.diag); break;
+    case FEMB_F_ELEM_VOLUME: r.elem_what = 0; r.count = ne; break;
+    case FEMB_F_ELEM_REF: r.elem_what = 1; r.count = ne * d * d; break;
+    case FEMB_F_ELEM_PHI: r.elem_what = 2; r.count = ne; break;
+    case FEMB_F_ELEM_H: need_implicit(); r.elem_what = 3; r.count = ne * d * d; break;
+    default: throw ArgError("unknown field id");
+  }
+  return r;
+}
+
+int femb_get(femb_object* o, int32_t field, void* host, size_t bytes) {
+  FEMB_TRY
+  if (!o || !host) throw ArgError("femb_get: NULL argument");
+  FEMB_CUDA(cudaSetDevice(o->device));
+  const FieldRef r = resolve(o, field);
+  if (bytes != r.count * sizeof(float)) throw ArgError("femb_get: byte count does not match the field size");
+  o->ensure_stage(r.count);
+  if (r.vec)
+    launch_pack_vertex(o->cfg, o->dim, o->n_vert, o->d_new_of_old, r.vec, r.comp0, r.ncomp, o->d_stage);
+  else
+    launch_pack_elem(o->cfg, o->dim, o->n_elem, o->d_slot_of_elem, o->e, o->h, o->d_phi, r.elem_what, o->d_stage);
+  FEMB_CUDA(cudaMemcpyAsync(host, o->d_stage, bytes, cudaMemcpyDeviceToHost, o->stream));
+  FEMB_CUDA(cudaStreamSynchronize(o->stream));
+  FEMB_CATCH
+}
+
+int femb_set(femb_object* o, int32_t field, const void* host, size_t bytes) {
+  FEMB_TRY
+  if (!o || !host) throw ArgError("femb_set: NULL argument");
+  FEMB_CUDA(cudaSetDevice(o->device));
+  const FieldRef r = resolve(o, field);
+  if (!r.vec) throw ArgError("femb_set: element fields are read-only");
+  if (field == FEMB_F_REF_POS) throw ArgError("femb_set: ref_pos is read-only");
+  if (bytes != r.count * sizeof(float)) throw ArgError("femb_set: byte count does not match the field size");
+  o->ensure_stage(r.count);
+  FEMB_CUDA(cudaMemcpyAsync(o->d_stage, host, bytes, cudaMemcpyHostToDevice, o->stream));
+  launch_unpack_vertex(o->cfg, o->dim, o->n_vert, o->d_new_of_old, o->d_stage, r.comp0, r.ncomp, r.vec);
+  // the staging buffer is reused by the next call: make the copy-in complete before returning
+  FEMB_CUDA(cudaStreamSynchronize(o->stream));
+  FEMB_CATCH
+}
+
+// ---- host-only tiling ------------------------------------------------------
+struct femb_tiling {
+  Tiling t;
+};
+
+int femb_tiling_build(int32_t dim, int32_t n_vert, int32_t n_elem, const float* verts, const int32_t* elems,
+                      int32_t tile_elems, femb_tiling** out) {
+  FEMB_TRY
+  if (!out) throw ArgError("NULL out");
+  *out = nullptr;
+  femb_tiling* h = new femb_tiling();
+  const std::string err = build_tiling(dim, n_vert, n_elem, verts, elems, tile_elems, h->t);
+  if (!err.empty()) { delete h; throw ArgError(err); }
+  *out = h;
+  FEMB_CATCH
+}
+
+int femb_tiling_destroy(femb_tiling* t) {
+  delete t;
+  return FEMB_OK;
+}
+
+int femb_tiling_info(const femb_tiling* t, femb_info* out) {
+  FEMB_TRY
+  if (!t || !out) throw ArgError("NULL argument");
+  fill_info(t->t, out);
+  FEMB_CATCH
+}
+
+int64_t femb_tiling_get(const femb_tiling* h, int32_t what, void* out, int64_t cap) {
+  if (!h) return -1;
+  const Tiling& t = h->t;
+  const void* src = nullptr;
+  int64_t count = 0;
+  size_t esz = 4;
+  switch (what) {
+    case 0: src = t.new_of_old.data(); count = (int64_t)t.new_of_old.size(); break;
+    case 1: src = t.slot_of_elem.data(); count = (int64_t)t.slot_of_elem.size(); break;
+    case 2: src = t.tiles.data(); count = (int64_t)t.tiles.size() * 12; break;
+    case 3: src = t.lv.data(); count = (int64_t)t.lv.size() * 2; break;
+    case 4: src = t.jds.data(); count = (int64_t)t.jds.size(); esz = 2; break;
+    case 5: src = t.rounds.data(); count = (int64_t)t.rounds.size(); break;
+    case 6: src = t.lidx.data(); count = (int64_t)t.lidx.size(); break;
+    case 7: src = t.bptr.data(); count = (int64_t)t.bptr.size(); break;
+    default: return -1;
+  }
+  if (out && cap > 0) std::memcpy(out, src, (size_t)std::min(cap, count) * esz);
+  return count;
+}
+
+}  // extern "C"

@@ -1,0 +1,180 @@
+// dev.cuh -- device-side views and small dense algebra shared by the kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+
+#include "tiling.h"
+
+namespace femb {
+
+// Device view of the tiling + element planes (all pointers are device memory).
+struct DevTiling {
+  const TileDesc* tiles;
+  const LocalVert* lv;
+  const uint16_t* jds;
+  const uint32_t* rounds;
+  const int32_t* bptr;   // [n_boundary+1]
+  int n_tiles, n_interior, n_boundary, n_vert, n_slots;
+  int stage_stride;      // floats per staging plane (>= max tile elems, multiple of 32)
+  int max_lv;
+};
+
+// Element planes, one float4 per slot per plane.
+//   3D  e0 = {idx01, idx23, V,   r00}  e1 = {r01, r02, r10, r11}  e2 = {r12, r20, r21, r22}
+//   2D  e0 = {idx01, idx2,  V,   r00}  e1 = {r01, r10, r11, 0}
+//   3D  h0 = {idx01, idx23, h00, h01}  h1 = {h02, h10, h11, h12}  h2 = {h20, h21, h22, 0}
+//   2D  h0 = {idx01, idx2,  h00, h01}  h1 = {h10, h11, 0,   0}
+struct Planes {
+  float4* p0;
+  float4* p1;
+  float4* p2;
+};
+
+struct Blocks {            // circle_blocks.py:6-25
+  const float4* data;      // {cx, cy, cz, radius}
+  int count;
+};
+
+struct Reduce {            // deterministic two-stage reductions
+  double* partial;         // [n_partial_blocks] per-CTA partial sums
+  int n;
+};
+
+template <int D>
+struct Mat {
+  float m[D][D];
+};
+
+template <int D>
+__device__ __forceinline__ float det(const Mat<D>& a);
+
+template <>
+__device__ __forceinline__ float det<2>(const Mat<2>& a) {
+  return a.m[0][0] * a.m[1][1] - a.m[0][1] * a.m[1][0];
+}
+
+// cofactor matrix C with inverse(A) = C^T / det(A), i.e. A^-T = C / det
+template <int D>
+__device__ __forceinline__ void cofactor(const Mat<D>& a, Mat<D>& c);
+
+template <>
+__device__ __forceinline__ void cofactor<2>(const Mat<2>& a, Mat<2>& c) {
+  c.m[0][0] = a.m[1][1];
+  c.m[0][1] = -a.m[1][0];
+  c.m[1][0] = -a.m[0][1];
+  c.m[1][1] = a.m[0][0];
+}
+
+template <>
+__device__ __forceinline__ void cofactor<3>(const Mat<3>& a, Mat<3>& c) {
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      const int i1 = (i + 1) % 3, i2 = (i + 2) % 3, j1 = (j + 1) % 3, j2 = (j + 2) % 3;
+      c.m[i][j] = a.m[i1][j1] * a.m[i2][j2] - a.m[i2][j1] * a.m[i1][j2];
+    }
+}
+
+template <>
+__device__ __forceinline__ float det<3>(const Mat<3>& a) {
+  return a.m[0][0] * (a.m[1][1] * a.m[2][2] - a.m[2][1] * a.m[1][2]) -
+         a.m[1][0] * (a.m[0][1] * a.m[2][2] - a.m[2][1] * a.m[0][2]) +
+         a.m[2][0] * (a.m[0][1] * a.m[1][2] - a.m[1][1] * a.m[0][2]);
+}
+
+// c = a @ b, k ascending
+template <int D>
+__device__ __forceinline__ void matmul(const Mat<D>& a, const Mat<D>& b, Mat<D>& c) {
+#pragma unroll
+  for (int i = 0; i < D; ++i)
+#pragma unroll
+    for (int j = 0; j < D; ++j) {
+      float s = a.m[i][0] * b.m[0][j];
+#pragma unroll
+      for (int k = 1; k < D; ++k) s += a.m[i][k] * b.m[k][j];
+      c.m[i][j] = s;
+    }
+}
+
+// c = a @ b^T
+template <int D>
+__device__ __forceinline__ void matmul_nt(const Mat<D>& a, const Mat<D>& b, Mat<D>& c) {
+#pragma unroll
+  for (int i = 0; i < D; ++i)
+#pragma unroll
+    for (int j = 0; j < D; ++j) {
+      float s = a.m[i][0] * b.m[j][0];
+#pragma unroll
+      for (int k = 1; k < D; ++k) s += a.m[i][k] * b.m[j][k];
+      c.m[i][j] = s;
+    }
+}
+
+// c = a^T @ b
+template <int D>
+__device__ __forceinline__ void matmul_tn(const Mat<D>& a, const Mat<D>& b, Mat<D>& c) {
+#pragma unroll
+  for (int i = 0; i < D; ++i)
+#pragma unroll
+    for (int j = 0; j < D; ++j) {
+      float s = a.m[0][i] * b.m[0][j];
+#pragma unroll
+      for (int k = 1; k < D; ++k) s += a.m[k][i] * b.m[k][j];
+      c.m[i][j] = s;
+    }
+}
+
+__device__ __forceinline__ float comp(const float4& v, int k) {
+  return k == 0 ? v.x : (k == 1 ? v.y : (k == 2 ? v.z : v.w));
+}
+
+template <int D>
+__device__ __forceinline__ void unpack_ref(const float4& e0, const float4& e1, const float4& e2, Mat<D>& r);
+
+template <>
+__device__ __forceinline__ void unpack_ref<3>(const float4& e0, const float4& e1, const float4& e2, Mat<3>& r) {
+  r.m[0][0] = e0.w; r.m[0][1] = e1.x; r.m[0][2] = e1.y;
+  r.m[1][0] = e1.z; r.m[1][1] = e1.w; r.m[1][2] = e2.x;
+  r.m[2][0] = e2.y; r.m[2][1] = e2.z; r.m[2][2] = e2.w;
+}
+
+template <>
+__device__ __forceinline__ void unpack_ref<2>(const float4& e0, const float4& e1, const float4&, Mat<2>& r) {
+  r.m[0][0] = e0.w; r.m[0][1] = e1.x;
+  r.m[1][0] = e1.y; r.m[1][1] = e1.z;
+}
+
+template <int D>
+__device__ __forceinline__ void unpack_h(const float4& h0, const float4& h1, const float4& h2, Mat<D>& h);
+
+template <>
+__device__ __forceinline__ void unpack_h<3>(const float4& h0, const float4& h1, const float4& h2, Mat<3>& h) {
+  h.m[0][0] = h0.z; h.m[0][1] = h0.w; h.m[0][2] = h1.x;
+  h.m[1][0] = h1.y; h.m[1][1] = h1.z; h.m[1][2] = h1.w;
+  h.m[2][0] = h2.x; h.m[2][1] = h2.y; h.m[2][2] = h2.z;
+}
+
+template <>
+__device__ __forceinline__ void unpack_h<2>(const float4& h0, const float4& h1, const float4&, Mat<2>& h) {
+  h.m[0][0] = h0.z; h.m[0][1] = h0.w;
+  h.m[1][0] = h1.x; h.m[1][1] = h1.y;
+}
+
+// Ds[:, j] = p_{j+1} - p_0 from the staged tile vertices (explicit.py:11-16)
+template <int D>
+__device__ __forceinline__ void edge_matrix(const float4* sv, uint32_t w0, uint32_t w1, Mat<D>& x) {
+  const float4 p0 = sv[w0 & 0xffffu];
+  const float4 p1 = sv[w0 >> 16];
+  const float4 p2 = sv[w1 & 0xffffu];
+  x.m[0][0] = p1.x - p0.x; x.m[1][0] = p1.y - p0.y;
+  x.m[0][1] = p2.x - p0.x; x.m[1][1] = p2.y - p0.y;
+  if constexpr (D == 3) {
+    const float4 p3 = sv[w1 >> 16];
+    x.m[2][0] = p1.z - p0.z;
+    x.m[2][1] = p2.z - p0.z;
+    x.m[0][D - 1] = p3.x - p0.x; x.m[1][D - 1] = p3.y - p0.y; x.m[2][D - 1] = p3.z - p0.z;
+  }
+}
+
+}  // namespace femb

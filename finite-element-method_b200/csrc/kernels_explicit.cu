@@ -1,0 +1,321 @@
+// kernels_explicit.cu -- setup (object.py:345-362), explicit element gradient
+// (explicit.py:8-49), energy (explicit_auto_diff.py:8-30) and the symplectic-Euler
+// vertex update with walls and circle blocks (kinematic.py:9-45), hand-written
+// for sm_100a on the tile layout of tiling.h.
+#include <atomic>
+#include <stdexcept>
+#include <string>
+
+#include "launch.h"
+#include "tile_pass.cuh"
+
+namespace femb {
+
+static std::atomic<uint64_t> g_launches{0};
+uint64_t launch_count() { return g_launches.load(); }
+void note_launch(const char* what, cudaStream_t) {
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  const cudaError_t err = cudaGetLastError();
+  if (err != cudaSuccess) throw std::runtime_error(std::string(what) + ": " + cudaGetErrorString(err));
+}
+
+// ---------------------------------------------------------------------------
+// vertex update shared by the fused step, the stand-alone kinematic kernel
+// ---------------------------------------------------------------------------
+template <int D>
+__device__ __forceinline__ void kinematic_update(float4& p, float4& v, const float (&g)[D], const KinArgs& k) {
+  float pos[3] = {p.x, p.y, p.z};
+  float vel[3] = {v.x, v.y, v.z};
+  const float m = p.w;
+#pragma unroll
+  for (int i = 0; i < D; ++i) {
+    // vel += (acc + 9.8*g_dir - grad/mass) * dt, acc == 0     (kinematic.py:15-20)
+    vel[i] += (k.g98[i] - g[i] / m) * k.dt;
+    vel[i] *= k.damp;                                    // kinematic.py:23
+    if (pos[i] < 0.f && vel[i] < 0.f) vel[i] = 0.f;      // kinematic.py:25-30 (old positions)
+    if (pos[i] > 1.f && vel[i] > 0.f) vel[i] = 0.f;
+  }
+  for (int b = 0; b < k.blocks.count; ++b) {             // kinematic.py:32-41
+    const float4 blk = k.blocks.data[b];
+    if (blk.w <= 0.f) continue;
+    const float c[3] = {blk.x, blk.y, blk.z};
+    float disp[3], nsq = 0.f, vdc = 0.f, vdd = 0.f;
+#pragma unroll
+    for (int i = 0; i < D; ++i) {
+      disp[i] = pos[i] - c[i];
+      nsq += disp[i] * disp[i];
+      vdc += vel[i] * (c[i] - pos[i]);
+      vdd += vel[i] * disp[i];
+    }
+    if (sqrtf(nsq) < blk.w && vdc > 0.f) {
+#pragma unroll
+      for (int i = 0; i < D; ++i) vel[i] -= vdd * disp[i] / nsq;
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < D; ++i) pos[i] += vel[i] * k.dt;   // kinematic.py:43
+  p.x = pos[0]; p.y = pos[1]; if (D == 3) p.z = pos[2];
+  v.x = vel[0]; v.y = vel[1]; if (D == 3) v.z = vel[2];
+}
+
+// ---------------------------------------------------------------------------
+// setup: Dm^-1, volume, lumped mass.  Contraction-free arithmetic (__fmul_rn /
+// __fsub_rn ...) so ref and volume are bit-identical to the fp32 oracle.
+// ---------------------------------------------------------------------------
+template <int D>
+struct OpSetup {
+  static constexpr int BLOCK = 256, MIN_CTAS = 2, NSTAGE = 1, GATHER = G_UNIFORM;
+  static constexpr bool REDUCE = false;
+  struct Args {
+    Planes e;
+    const uint32_t* lidx;
+    VertexState vs;
+    Material mat;
+  };
+  __device__ static bool early_exit(const Args&) { return false; }
+  __device__ static float w0() { return 1.f; }
+  __device__ static float4* partial_buf(const Args& a) { return a.vs.partial; }
+  __device__ static double* red_buf(const Args&) { return nullptr; }
+  __device__ static float4 load_vertex(const Args& a, int gid) { return a.vs.pos[gid]; }
+
+  __device__ static void element(const Args& a, int slot, const float4* sv, float (&out)[NSTAGE], float&) {
+    const uint32_t w0 = a.lidx[2 * slot], w1 = a.lidx[2 * slot + 1];
+    Mat<D> r;
+    edge_matrix<D>(sv, w0, w1, r);  // plain subtractions: nothing to contract
+    float vol;
+    Mat<D> inv;
+    if constexpr (D == 2) {
+      // object.py:388-389 ; 2x2 adjugate inverse
+      const float cross = __fsub_rn(__fmul_rn(r.m[0][0], r.m[1][1]), __fmul_rn(r.m[1][0], r.m[0][1]));
+      vol = fabsf(cross) / 2.f;
+      const float dt = __fsub_rn(__fmul_rn(r.m[0][0], r.m[1][1]), __fmul_rn(r.m[0][1], r.m[1][0]));
+      const float id = __fdiv_rn(1.f, dt);
+      inv.m[0][0] = __fmul_rn(r.m[1][1], id);
+      inv.m[0][1] = __fmul_rn(-r.m[0][1], id);
+      inv.m[1][0] = __fmul_rn(-r.m[1][0], id);
+      inv.m[1][1] = __fmul_rn(r.m[0][0], id);
+    } else {
+      // object.py:390-391: (1/6)|p0 . (p1 x p2)| with p_j = column j
+      const float cx = __fsub_rn(__fmul_rn(r.m[1][1], r.m[2][2]), __fmul_rn(r.m[2][1], r.m[1][2]));
+      const float cy = __fsub_rn(__fmul_rn(r.m[2][1], r.m[0][2]), __fmul_rn(r.m[0][1], r.m[2][2]));
+      const float cz = __fsub_rn(__fmul_rn(r.m[0][1], r.m[1][2]), __fmul_rn(r.m[1][1], r.m[0][2]));
+      const float dot = __fadd_rn(__fadd_rn(__fmul_rn(r.m[0][0], cx), __fmul_rn(r.m[1][0], cy)), __fmul_rn(r.m[2][0], cz));
+      vol = __fmul_rn((float)(1.0 / 6.0), fabsf(dot));
+      const float t0 = __fsub_rn(__fmul_rn(r.m[1][1], r.m[2][2]), __fmul_rn(r.m[2][1], r.m[1][2]));
+      const float t1 = __fsub_rn(__fmul_rn(r.m[0][1], r.m[2][2]), __fmul_rn(r.m[2][1], r.m[0][2]));
+      const float t2 = __fsub_rn(__fmul_rn(r.m[0][1], r.m[1][2]), __fmul_rn(r.m[1][1], r.m[0][2]));
+      const float dt = __fadd_rn(__fsub_rn(__fmul_rn(r.m[0][0], t0), __fmul_rn(r.m[1][0], t1)), __fmul_rn(r.m[2][0], t2));
+      const float id = __fdiv_rn(1.f, dt);
+#pragma unroll
+      for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+          const int i1 = (i + 1) % 3, i2 = (i + 2) % 3, j1 = (j + 1) % 3, j2 = (j + 2) % 3;
+          inv.m[j][i] = __fmul_rn(id, __fsub_rn(__fmul_rn(r.m[i1][j1], r.m[i2][j2]), __fmul_rn(r.m[i2][j1], r.m[i1][j2])));
+        }
+    }
+    float4 e0, e1, e2;
+    e0.x = __uint_as_float(w0); e0.y = __uint_as_float(w1); e0.z = vol; e0.w = inv.m[0][0];
+    if constexpr (D == 3) {
+      e1 = make_float4(inv.m[0][1], inv.m[0][2], inv.m[1][0], inv.m[1][1]);
+      e2 = make_float4(inv.m[1][2], inv.m[2][0], inv.m[2][1], inv.m[2][2]);
+      a.e.p2[slot] = e2;
+    } else {
+      e1 = make_float4(inv.m[0][1], inv.m[1][0], inv.m[1][1], 0.f);
+    }
+    a.e.p0[slot] = e0;
+    a.e.p1[slot] = e1;
+    // mass[v] += 1/(dim+1) * V * rho          (object.py:358-360)
+    out[0] = __fmul_rn(__fmul_rn((float)(1.0 / (D + 1)), vol), a.mat.rho);
+  }
+  __device__ static void vertex(const Args& a, int gid, float4, const float (&acc)[D], float&) {
+    a.vs.pos[gid].w = acc[0];
+  }
+};
+
+// ---------------------------------------------------------------------------
+// explicit element gradient / fused step / energy
+// ---------------------------------------------------------------------------
+template <int D, int MODE>
+struct OpExplicit {
+  static constexpr int BLOCK = 256, MIN_CTAS = 2, NSTAGE = D * D, GATHER = G_STAR;
+  static constexpr bool REDUCE = (MODE == EX_ENERGY);
+  struct Args {
+    Planes e;
+    VertexState vs;
+    Material mat;
+    KinArgs kin;
+    float* phi;
+    double* red;
+  };
+  __device__ static bool early_exit(const Args&) { return false; }
+  __device__ static float w0() { return 0.f; }
+  __device__ static float4* partial_buf(const Args& a) { return a.vs.partial; }
+  __device__ static double* red_buf(const Args& a) { return a.red; }
+  __device__ static float4 load_vertex(const Args& a, int gid) { return a.vs.pos[gid]; }
+
+  __device__ static void element(const Args& a, int slot, const float4* sv, float (&out)[NSTAGE], float& red) {
+    const float4 e0 = a.e.p0[slot];
+    const float4 e1 = a.e.p1[slot];
+    float4 e2 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if constexpr (D == 3) e2 = a.e.p2[slot];
+    Mat<D> R, X, F, C;
+    unpack_ref<D>(e0, e1, e2, R);
+    edge_matrix<D>(sv, __float_as_uint(e0.x), __float_as_uint(e0.y), X);  // explicit.py:11-16
+    matmul<D>(X, R, F);                                                   // F = X @ R_inv (19)
+    cofactor<D>(F, C);                                                    // F^-T = C / det
+    const float J = det<D>(F);
+    const float log_j = logf(J);                                          // explicit.py:24 (no clamp)
+    const float inv_j = 1.f / J;
+    const float V = e0.z;
+    // P = mu F - mu F^-T + lambda log(J) F^-T                            (explicit.py:25)
+    const float cf = (a.mat.lambda * log_j - a.mat.mu) * inv_j;
+    Mat<D> P, G;
+#pragma unroll
+    for (int i = 0; i < D; ++i)
+#pragma unroll
+      for (int j = 0; j < D; ++j) P.m[i][j] = a.mat.mu * F.m[i][j] + cf * C.m[i][j];
+    matmul_nt<D>(P, R, G);                                                // @ R_inv^T
+#pragma unroll
+    for (int j = 0; j < D; ++j)
+#pragma unroll
+      for (int i = 0; i < D; ++i) out[j * D + i] = G.m[i][j] * V;        // force *= V (28)
+    if (MODE == EX_ENERGY) {
+      // explicit_auto_diff.py:25-30
+      float tr = 0.f;
+#pragma unroll
+      for (int i = 0; i < D; ++i)
+#pragma unroll
+        for (int j = 0; j < D; ++j) tr += F.m[i][j] * F.m[i][j];
+      float phi = a.mat.mu / 2.f * (tr - (float)D);
+      phi -= a.mat.mu * log_j;
+      phi += a.mat.lambda / 2.f * log_j * log_j;
+      const float pv = phi * V;
+      a.phi[slot] = pv;
+      red += pv;
+    }
+  }
+
+  __device__ static void vertex(const Args& a, int gid, float4 p, const float (&acc)[D], float&) {
+    if (MODE == EX_GRAD) {
+      float4 f = a.vs.force[gid];                                         // force[v] += f (explicit.py:42-49)
+      f.x += acc[0]; f.y += acc[1]; if (D == 3) f.z += acc[D - 1];
+      a.vs.force[gid] = f;
+    } else if (MODE == EX_ENERGY) {
+      a.vs.grad[gid] = make_float4(acc[0], acc[1], D == 3 ? acc[D - 1] : 0.f, 0.f);
+    } else {
+      float4 v = a.vs.vel[gid];
+      kinematic_update<D>(p, v, acc, a.kin);
+      a.vs.pos[gid] = p;
+      a.vs.vel[gid] = v;
+    }
+  }
+};
+
+template <int D>
+__global__ void __launch_bounds__(256) k_kinematic(int n, VertexState vs, KinArgs kin, int use_grad) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float4 p = vs.pos[i], v = vs.vel[i];
+  const float4 gsrc = use_grad ? vs.grad[i] : vs.force[i];
+  float g[D];
+  g[0] = gsrc.x; g[1] = gsrc.y; if (D == 3) g[D - 1] = gsrc.z;
+  kinematic_update<D>(p, v, g, kin);
+  vs.pos[i] = p;
+  vs.vel[i] = v;
+  if (!use_grad) vs.force[i] = make_float4(0.f, 0.f, 0.f, 0.f);           // kinematic.py:44-45
+}
+
+// advect_implicit, implicit.py:407-437
+template <int D>
+__global__ void __launch_bounds__(256) k_advect_implicit(int n, VertexState vs, KinArgs k) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n) return;
+  float4 p4 = vs.pos[idx], v4 = vs.vel[idx], g4 = vs.vel_g[idx];
+  float pos[3] = {p4.x, p4.y, p4.z}, vel[3] = {v4.x, v4.y, v4.z}, vg[3] = {g4.x, g4.y, g4.z}, v[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+  for (int i = 0; i < D; ++i) {
+    vg[i] += k.g98[i] * k.dt;      // 409
+    vel[i] *= k.damp;              // 410
+    vg[i] *= k.damp;               // 411
+    v[i] = vel[i] + vg[i];         // 412
+    if (pos[i] < 0.f && v[i] < 0.f) { vel[i] = 0.f; vg[i] = 0.f; v[i] = 0.f; }   // 415-418
+    if (pos[i] > 1.f && v[i] > 0.f) { vel[i] = 0.f; v[i] = 0.f; }                 // 420-423 (vel_g kept)
+  }
+  for (int b = 0; b < k.blocks.count; ++b) {   // 424-435
+    const float4 blk = k.blocks.data[b];
+    if (blk.w <= 0.f) continue;
+    const float c[3] = {blk.x, blk.y, blk.z};
+    float disp[3], nsq = 0.f, vdc = 0.f, d_v = 0.f, d_vel = 0.f, d_vg = 0.f;
+#pragma unroll
+    for (int i = 0; i < D; ++i) {
+      disp[i] = pos[i] - c[i];
+      nsq += disp[i] * disp[i];
+      vdc += v[i] * (c[i] - pos[i]);
+      d_v += v[i] * disp[i];
+      d_vel += vel[i] * disp[i];
+      d_vg += vg[i] * disp[i];
+    }
+    if (sqrtf(nsq) < blk.w && vdc > 0.f) {
+#pragma unroll
+      for (int i = 0; i < D; ++i) {
+        v[i] -= d_v * disp[i] / nsq;
+        vel[i] -= d_vel * disp[i] / nsq;
+        vg[i] -= d_vg * disp[i] / nsq;
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < D; ++i) pos[i] += v[i] * k.dt;   // 437
+  p4.x = pos[0]; p4.y = pos[1]; if (D == 3) p4.z = pos[2];
+  v4.x = vel[0]; v4.y = vel[1]; if (D == 3) v4.z = vel[2];
+  g4.x = vg[0]; g4.y = vg[1]; if (D == 3) g4.z = vg[2];
+  vs.pos[idx] = p4; vs.vel[idx] = v4; vs.vel_g[idx] = g4;
+}
+
+// ---------------------------------------------------------------------------
+// launchers
+// ---------------------------------------------------------------------------
+void launch_setup(int dim, const LaunchCfg& c, const DevTiling& tl, Planes e, const uint32_t* lidx,
+                  VertexState vs, Material mat) {
+  if (dim == 3) {
+    OpSetup<3>::Args a{e, lidx, vs, mat};
+    run_tile_pass<3, OpSetup<3>>("setup<3>", c, tl, a);
+  } else {
+    OpSetup<2>::Args a{e, lidx, vs, mat};
+    run_tile_pass<2, OpSetup<2>>("setup<2>", c, tl, a);
+  }
+}
+
+template <int D, int MODE>
+static void launch_explicit_t(const LaunchCfg& c, const DevTiling& tl, Planes e, VertexState vs, Material mat,
+                              KinArgs kin, float* phi, double* red) {
+  typename OpExplicit<D, MODE>::Args a{e, vs, mat, kin, phi, red};
+  run_tile_pass<D, OpExplicit<D, MODE>>("explicit", c, tl, a);
+}
+
+void launch_explicit(int dim, int mode, const LaunchCfg& c, const DevTiling& tl, Planes e, VertexState vs,
+                     Material mat, KinArgs kin, float* phi, double* red) {
+#define FEMB_CASE(D, M) \
+  if (dim == D && mode == M) return launch_explicit_t<D, M>(c, tl, e, vs, mat, kin, phi, red);
+  FEMB_CASE(3, EX_GRAD) FEMB_CASE(3, EX_STEP) FEMB_CASE(3, EX_ENERGY)
+  FEMB_CASE(2, EX_GRAD) FEMB_CASE(2, EX_STEP) FEMB_CASE(2, EX_ENERGY)
+#undef FEMB_CASE
+  throw std::runtime_error("launch_explicit: bad dim/mode");
+}
+
+void launch_kinematic(int dim, const LaunchCfg& c, int n_vert, VertexState vs, KinArgs kin, int use_grad) {
+  const int nb = (n_vert + 255) / 256;
+  if (dim == 3) k_kinematic<3><<<nb, 256, 0, c.stream>>>(n_vert, vs, kin, use_grad);
+  else k_kinematic<2><<<nb, 256, 0, c.stream>>>(n_vert, vs, kin, use_grad);
+  note_launch("kinematic", c.stream);
+}
+
+void launch_advect_implicit(int dim, const LaunchCfg& c, int n_vert, VertexState vs, KinArgs kin) {
+  const int nb = (n_vert + 255) / 256;
+  if (dim == 3) k_advect_implicit<3><<<nb, 256, 0, c.stream>>>(n_vert, vs, kin);
+  else k_advect_implicit<2><<<nb, 256, 0, c.stream>>>(n_vert, vs, kin);
+  note_launch("advect_implicit", c.stream);
+}
+
+}  // namespace femb

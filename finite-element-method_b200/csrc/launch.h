@@ -1,0 +1,99 @@
+// launch.h -- host-callable launchers implemented in kernels.cu (one per kernel family).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+
+#include "dev.cuh"
+
+namespace femb {
+
+struct VertexState {       // SoA-of-float4 vertex arrays in the library's numbering
+  float4* pos;             // {x, y, z, mass}           particles.pos / .mass
+  float4* vel;             // particles.vel
+  float4* vel_g;           // particles.vel_g  (implicit objects only)
+  float4* force;           // particles.force  (+dE/dx)
+  float4* grad;            // particles.pos.grad
+  float4* partial;         // [n_partials] boundary partial sums
+  float4* partial2;        // second partial buffer (implicit assemble)
+};
+
+struct Material {
+  float mu, lambda, rho, damping;
+};
+
+struct KinArgs {           // kinematic.py:14-45 / implicit.py:407-437 constants
+  float dt;
+  float g98[3];            // 9.8f * g_dir
+  float damp;              // expf(-dt * damping)
+  Blocks blocks;
+};
+
+struct ImplicitVecs {      // object.py:83-93 vectors, float4 per vertex
+  float4 *b, *x, *past_x, *d, *r, *q, *atb, *tmp, *diag;
+};
+
+struct SolveScalars {      // device-resident solver state (one per object)
+  double delta_new, delta_old, dq, err, p_err;
+  float alpha, beta;
+  int iters, done, terminal, action, first;
+};
+
+enum ExplicitMode { EX_GRAD = 0, EX_STEP = 1, EX_ENERGY = 2 };
+
+struct LaunchCfg {
+  cudaStream_t stream;
+  int block;               // threads per CTA of the tile kernels
+  int smem;                // dynamic shared memory of the tile kernels
+  int sms;
+  int device;
+};
+
+// setup: Dm^-1, volume -> element planes; lumped mass -> pos.w   (object.py:345-362)
+void launch_setup(int dim, const LaunchCfg& c, const DevTiling& tl, Planes e, const uint32_t* lidx,
+                  VertexState vs, Material mat);
+// explicit tile + boundary pass
+void launch_explicit(int dim, int mode, const LaunchCfg& c, const DevTiling& tl, Planes e, VertexState vs,
+                     Material mat, KinArgs kin, float* phi, double* red);
+void launch_kinematic(int dim, const LaunchCfg& c, int n_vert, VertexState vs, KinArgs kin, int use_grad);
+void launch_advect_implicit(int dim, const LaunchCfg& c, int n_vert, VertexState vs, KinArgs kin);
+// implicit: H_e planes + b ; diag(A)
+void launch_implicit_assemble(int dim, const LaunchCfg& c, const DevTiling& tl, Planes e, Planes h,
+                              VertexState vs, Material mat, float dt, ImplicitVecs iv);
+void launch_implicit_diag(int dim, const LaunchCfg& c, const DevTiling& tl, Planes h, VertexState vs,
+                          float dt, ImplicitVecs iv);
+// out = A in / A^T in ; optional fused dot <dotv, out> or residual r = b - out with ||r||^2
+enum ApplyEpilogue { AP_PLAIN = 0, AP_DOT = 1, AP_RESID = 2 };
+void launch_apply(int dim, const LaunchCfg& c, const DevTiling& tl, Planes h, VertexState vs, float dt,
+                  int transpose, const float4* in, float4* out, int epilogue, const float4* aux,
+                  float4* resid_out, double* red, const SolveScalars* sc);
+int reduce_slots(const DevTiling& tl, const LaunchCfg& c);  // doubles needed in a reduction buffer
+
+// CG / Jacobi vector kernels (all early-exit on sc->done)
+void launch_cg_init(const LaunchCfg& c, int n_vert, ImplicitVecs iv, const float4* rhs, const float4* opx,
+                    double* red, SolveScalars* sc, float tol, int max_iter);
+void launch_cg_alpha(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc);
+void launch_cg_update_xr(const LaunchCfg& c, int n_vert, ImplicitVecs iv, double* red, SolveScalars* sc);
+void launch_cg_beta(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc, float tol, int max_iter);
+void launch_cg_update_d(const LaunchCfg& c, int n_vert, ImplicitVecs iv, const SolveScalars* sc);
+void launch_jacobi_decide(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc, float tol,
+                          int max_iter);
+void launch_jacobi_update(const LaunchCfg& c, int n_vert, ImplicitVecs iv, SolveScalars* sc);
+void launch_scalars_reset(const LaunchCfg& c, SolveScalars* sc);
+
+// misc vector ops
+void launch_copy_xyz(const LaunchCfg& c, int n, const float4* src, float4* dst);           // dst.xyz = src.xyz
+void launch_scale_xyz(const LaunchCfg& c, int n, const float4* src, float4* dst, float s); // dst.xyz = s*src.xyz
+void launch_fill(const LaunchCfg& c, int n, float4* dst, float4 v);
+void launch_reduce_final(const LaunchCfg& c, int n_red, const double* red, double* out);
+// host <-> device field marshalling in the caller's ordering
+void launch_pack_vertex(const LaunchCfg& c, int dim, int n_vert, const int32_t* new_of_old, const float4* src,
+                        int comp0, int ncomp, float* dst);
+void launch_unpack_vertex(const LaunchCfg& c, int dim, int n_vert, const int32_t* new_of_old, const float* src,
+                          int comp0, int ncomp, float4* dst);
+void launch_pack_elem(const LaunchCfg& c, int dim, int n_elem, const int32_t* slot_of_elem, Planes e, Planes h,
+                      const float* phi, int what, float* dst);
+
+uint64_t launch_count();
+void note_launch(const char* what, cudaStream_t s);  // counts + checks cudaGetLastError (throws std::runtime_error)
+
+}  // namespace femb

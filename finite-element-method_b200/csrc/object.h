@@ -1,0 +1,84 @@
+// object.h -- the host-side object behind the opaque femb_object handle.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/femb200.h"
+#include "launch.h"
+#include "tiling.h"
+
+namespace femb {
+
+struct CudaError : std::runtime_error {
+  using std::runtime_error::runtime_error;
+};
+struct ArgError : std::runtime_error {
+  using std::runtime_error::runtime_error;
+};
+struct StateError : std::runtime_error {
+  using std::runtime_error::runtime_error;
+};
+struct LimitError : std::runtime_error {
+  using std::runtime_error::runtime_error;
+};
+
+inline void cuda_check(cudaError_t e, const char* what) {
+  if (e != cudaSuccess) throw CudaError(std::string(what) + ": " + cudaGetErrorString(e));
+}
+#define FEMB_CUDA(x) ::femb::cuda_check((x), #x)
+
+struct StepGraph {          // cached CUDA graph of n fused explicit steps
+  cudaGraphExec_t exec = nullptr;
+  float dt = 0.f, g[3] = {0, 0, 0}, damp = 0.f;
+  int n_steps = 0, blocks_version = -1;
+  uint64_t launches = 0;
+};
+
+}  // namespace femb
+
+struct femb_object {
+  int dim = 0, n_vert = 0, n_elem = 0, device = 0;
+  bool implicit = false;
+  femb::Material mat{};
+  femb::Tiling til;                 // host copy (maps kept for diagnostics)
+  femb::DevTiling dtl{};
+  femb::Planes e{}, h{};
+  uint32_t* d_lidx = nullptr;
+  femb::VertexState vs{};
+  float4* ref_pos = nullptr;
+  femb::ImplicitVecs iv{};
+  float* d_phi = nullptr;           // per slot
+  double* d_red = nullptr;
+  int red_slots = 0;
+  double* d_U = nullptr;
+  femb::SolveScalars* d_sc = nullptr;
+  femb::SolveScalars* h_sc = nullptr;  // pinned
+  int32_t* d_new_of_old = nullptr;
+  int32_t* d_slot_of_elem = nullptr;
+  float* d_stage = nullptr;         // marshalling buffer
+  size_t stage_floats = 0;
+  float4* d_blocks = nullptr;
+  int n_blocks = 0, blocks_version = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  femb::LaunchCfg cfg{};
+  femb::StepGraph graph;
+  std::vector<void*> allocs;
+  int64_t device_bytes = 0;
+
+  template <class T>
+  T* alloc(size_t count, bool zero = true) {
+    void* p = nullptr;
+    const size_t bytes = (count ? count : 1) * sizeof(T);
+    FEMB_CUDA(cudaMalloc(&p, bytes));
+    allocs.push_back(p);
+    device_bytes += (int64_t)bytes;
+    if (zero) FEMB_CUDA(cudaMemsetAsync(p, 0, bytes, stream));
+    return static_cast<T*>(p);
+  }
+  void ensure_stage(size_t floats);
+  femb::KinArgs kin_args(float dt, const float* g_dir) const;
+};

@@ -1,0 +1,279 @@
+// tiling.cpp -- builds the tile layout described in tiling.h (host only, OpenMP).
+#include "tiling.h"
+
+#include <algorithm>
+#include <atomic>
+#include <cmath>
+#include <cstring>
+#include <numeric>
+
+namespace femb {
+namespace {
+
+struct Rcb {
+  const float* c[3];
+  int dim;
+  int T;
+  int32_t* idx;
+  std::vector<char>* is_start;
+
+  void run(int lo, int hi) {
+    const int n = hi - lo;
+    (*is_start)[lo] = 1;
+    if (n <= T) return;
+    // aim for ~88% fill so that cuts can snap to coordinate gaps (planar tile faces)
+    const int Tf = T - T / 8;
+    const int k = std::max(2, (n + Tf - 1) / Tf);
+    const int kl = k / 2;
+    int m = lo + (int)((int64_t)n * kl / k);
+    // longest axis of the centroid bounding box
+    float mn[3], mx[3];
+    for (int a = 0; a < dim; ++a) { mn[a] = INFINITY; mx[a] = -INFINITY; }
+    for (int i = lo; i < hi; ++i)
+      for (int a = 0; a < dim; ++a) {
+        const float v = c[a][idx[i]];
+        mn[a] = std::min(mn[a], v);
+        mx[a] = std::max(mx[a], v);
+      }
+    int axis = 0;
+    for (int a = 1; a < dim; ++a)
+      if (mx[a] - mn[a] > mx[axis] - mn[axis]) axis = a;
+    const float* ca = c[axis];
+    auto less = [ca](int32_t x, int32_t y) { return ca[x] < ca[y] || (ca[x] == ca[y] && x < y); };
+    std::nth_element(idx + lo, idx + m, idx + hi, less);
+    // Snap the cut to a gap between distinct coordinates when the balance
+    // allows it: structured meshes then get planar tile faces.
+    const float pivot = ca[idx[m]];
+    int cl = (int)(std::partition(idx + lo, idx + m, [&](int32_t x) { return ca[x] < pivot; }) - idx);
+    int cr = (int)(std::partition(idx + m, idx + hi, [&](int32_t x) { return ca[x] == pivot; }) - idx);
+    auto ok = [&](int cut) {
+      const int64_t nl = cut - lo, nr = hi - cut;
+      return nl > 0 && nr > 0 && nl <= (int64_t)kl * T && nr <= (int64_t)(k - kl) * T;
+    };
+    int best = -1;
+    if (ok(cl)) best = cl;
+    if (ok(cr) && (best < 0 || std::abs(cr - m) < std::abs(best - m))) best = cr;
+    if (best >= 0) m = best;
+    if (n > (1 << 16)) {
+#pragma omp task firstprivate(lo, m)
+      run(lo, m);
+#pragma omp task firstprivate(m, hi)
+      run(m, hi);
+#pragma omp taskwait
+    } else {
+      run(lo, m);
+      run(m, hi);
+    }
+  }
+};
+
+}  // namespace
+
+std::string build_tiling(int dim, int n_vert, int n_elem, const float* verts,
+                         const int32_t* elems, int tile_elems, Tiling& t) {
+  if (dim != 2 && dim != 3) return "dim must be 2 or 3";
+  if (n_vert <= 0 || n_elem <= 0) return "empty mesh";
+  if (!verts || !elems) return "null mesh arrays";
+  if (tile_elems < 32 || tile_elems > 4096) return "tile_elems must be in [32, 4096]";
+  const int nc = dim + 1;
+  for (int64_t i = 0; i < (int64_t)n_elem * nc; ++i)
+    if (elems[i] < 0 || elems[i] >= n_vert) return "element index out of range";
+
+  t = Tiling();
+  t.dim = dim; t.nc = nc; t.n_vert = n_vert; t.n_elem = n_elem; t.T = tile_elems;
+
+  // 1. spatial key per element = lower corner of its bounding box.  All elements of one
+  //    structured cell share the key, so snapped cuts never split a cell.
+  std::vector<float> cen[3];
+  for (int a = 0; a < dim; ++a) cen[a].resize(n_elem);
+#pragma omp parallel for schedule(static)
+  for (int e = 0; e < n_elem; ++e)
+    for (int a = 0; a < dim; ++a) {
+      float s = INFINITY;
+      for (int c = 0; c < nc; ++c) s = std::min(s, verts[(int64_t)elems[(int64_t)e * nc + c] * dim + a]);
+      cen[a][e] = s;
+    }
+
+  // 2. recursive coordinate bisection -> element order + tile starts
+  std::vector<int32_t> order(n_elem);
+  std::iota(order.begin(), order.end(), 0);
+  std::vector<char> is_start(n_elem + 1, 0);
+  {
+    Rcb r;
+    for (int a = 0; a < 3; ++a) r.c[a] = a < dim ? cen[a].data() : nullptr;
+    r.dim = dim; r.T = tile_elems; r.idx = order.data(); r.is_start = &is_start;
+#pragma omp parallel
+#pragma omp single
+    r.run(0, n_elem);
+  }
+  for (int a = 0; a < dim; ++a) std::vector<float>().swap(cen[a]);
+  std::vector<int> tbeg;
+  for (int i = 0; i < n_elem; ++i)
+    if (is_start[i]) tbeg.push_back(i);
+  tbeg.push_back(n_elem);
+  const int nt = (int)tbeg.size() - 1;
+  t.n_tiles = nt;
+  t.tiles.assign(nt, TileDesc{});
+
+  // 3. per tile: sorted element list, unique vertices, tile-incidence count per vertex
+  std::vector<std::vector<int32_t>> tverts(nt);
+  std::vector<std::atomic<int32_t>> tcount(n_vert);
+  for (auto& a : tcount) a.store(0, std::memory_order_relaxed);
+#pragma omp parallel for schedule(dynamic, 8)
+  for (int ti = 0; ti < nt; ++ti) {
+    std::sort(order.begin() + tbeg[ti], order.begin() + tbeg[ti + 1]);
+    const int ne = tbeg[ti + 1] - tbeg[ti];
+    std::vector<int32_t>& v = tverts[ti];
+    v.resize((size_t)ne * nc);
+    for (int i = 0; i < ne; ++i)
+      for (int c = 0; c < nc; ++c) v[(size_t)i * nc + c] = elems[(int64_t)order[tbeg[ti] + i] * nc + c];
+    std::sort(v.begin(), v.end());
+    v.erase(std::unique(v.begin(), v.end()), v.end());
+    for (int32_t g : v) tcount[g].fetch_add(1, std::memory_order_relaxed);
+  }
+  for (int v = 0; v < n_vert; ++v)
+    if (tcount[v].load(std::memory_order_relaxed) == 0) return "mesh has a vertex that no element references";
+
+  // 4. per tile: in-tile valence, local order (valence descending, then old id)
+  std::vector<std::vector<int32_t>> tval(nt);   // valence in local order
+  std::vector<std::vector<int32_t>> tperm(nt);  // local order -> position in sorted-unique list
+#pragma omp parallel for schedule(dynamic, 8)
+  for (int ti = 0; ti < nt; ++ti) {
+    const std::vector<int32_t>& v = tverts[ti];
+    const int ne = tbeg[ti + 1] - tbeg[ti];
+    const int nl = (int)v.size();
+    std::vector<int32_t> val(nl, 0);
+    for (int i = 0; i < ne; ++i)
+      for (int c = 0; c < nc; ++c) {
+        const int32_t g = elems[(int64_t)order[tbeg[ti] + i] * nc + c];
+        val[std::lower_bound(v.begin(), v.end(), g) - v.begin()]++;
+      }
+    std::vector<int32_t>& p = tperm[ti];
+    p.resize(nl);
+    std::iota(p.begin(), p.end(), 0);
+    std::stable_sort(p.begin(), p.end(), [&](int32_t a, int32_t b) { return val[a] > val[b]; });
+    tval[ti].resize(nl);
+    int n_int = 0;
+    for (int l = 0; l < nl; ++l) {
+      tval[ti][l] = val[p[l]];
+      if (tcount[v[p[l]]].load(std::memory_order_relaxed) == 1) ++n_int;
+    }
+    TileDesc& d = t.tiles[ti];
+    d.n_elem = ne;
+    d.n_lv = nl;
+    d.n_rounds = nl ? tval[ti][0] : 0;
+    d.n_int = n_int;
+  }
+
+  // 5. offsets + vertex renumbering (serial, deterministic)
+  {
+    int64_t slot = 0, lvo = 0, jo = 0, ro = 0;
+    int ib = 0;
+    for (int ti = 0; ti < nt; ++ti) {
+      TileDesc& d = t.tiles[ti];
+      if (d.n_lv > 65535) return "tile has more than 65535 local vertices";
+      d.slot_off = (int32_t)slot; slot += (d.n_elem + 31) / 32 * 32;
+      d.lv_off = (int32_t)lvo;   lvo += d.n_lv;
+      d.jds_off = (int32_t)jo;   jo += (int64_t)d.n_elem * nc;
+      d.rounds_off = (int32_t)ro; ro += d.n_rounds;
+      d.int_base = ib;           ib += d.n_int;
+      t.max_tile_elems = std::max(t.max_tile_elems, d.n_elem);
+      t.max_lv = std::max(t.max_lv, d.n_lv);
+      t.max_rounds = std::max(t.max_rounds, d.n_rounds);
+      if (slot > INT32_MAX || jo > INT32_MAX) return "mesh too large for 32-bit slot offsets";
+    }
+    t.n_slots = (int)slot;
+    t.n_interior = ib;
+    t.n_boundary = n_vert - ib;
+    t.lv.resize(lvo);
+    t.jds.assign(jo, 0);
+    t.rounds.resize(ro);
+    t.lidx.assign((size_t)t.n_slots * 2, 0);
+    t.slot_of_elem.assign(n_elem, -1);
+    t.elem_of_slot.assign(t.n_slots, -1);
+  }
+  t.new_of_old.assign(n_vert, -1);
+  t.old_of_new.assign(n_vert, -1);
+  std::vector<int32_t> bcount(t.n_boundary, 0);
+  {
+    int nb = 0;
+    for (int ti = 0; ti < nt; ++ti) {
+      const TileDesc& d = t.tiles[ti];
+      int ni = 0;
+      for (int l = 0; l < d.n_lv; ++l) {
+        const int32_t g = tverts[ti][tperm[ti][l]];
+        if (tcount[g].load(std::memory_order_relaxed) == 1) {
+          t.new_of_old[g] = d.int_base + ni++;
+        } else {
+          if (t.new_of_old[g] < 0) t.new_of_old[g] = t.n_interior + nb++;
+          bcount[t.new_of_old[g] - t.n_interior]++;
+        }
+      }
+    }
+    if (nb != t.n_boundary) return "internal error: boundary count mismatch";
+  }
+  for (int v = 0; v < n_vert; ++v) t.old_of_new[t.new_of_old[v]] = v;
+  t.bptr.assign(t.n_boundary + 1, 0);
+  for (int b = 0; b < t.n_boundary; ++b) t.bptr[b + 1] = t.bptr[b] + bcount[b];
+  t.n_partials = t.bptr[t.n_boundary];
+  {
+    std::vector<int32_t> cursor(t.bptr.begin(), t.bptr.end() - 1);
+    for (int ti = 0; ti < nt; ++ti) {
+      const TileDesc& d = t.tiles[ti];
+      for (int l = 0; l < d.n_lv; ++l) {
+        const int32_t g = tverts[ti][tperm[ti][l]];
+        LocalVert& e = t.lv[(size_t)d.lv_off + l];
+        e.gid = t.new_of_old[g];
+        e.part = e.gid >= t.n_interior ? cursor[e.gid - t.n_interior]++ : -1;
+      }
+    }
+  }
+
+  // 6. per tile: packed local indices, slots, JDS incidence lists
+#pragma omp parallel for schedule(dynamic, 8)
+  for (int ti = 0; ti < nt; ++ti) {
+    const TileDesc& d = t.tiles[ti];
+    const std::vector<int32_t>& v = tverts[ti];
+    const std::vector<int32_t>& p = tperm[ti];
+    const int nl = d.n_lv;
+    std::vector<int32_t> local_of_sorted(nl);
+    for (int l = 0; l < nl; ++l) local_of_sorted[p[l]] = l;
+    // incidence lists in local order; entries appended corner-major so that
+    // each list is sorted by (corner, slot)
+    std::vector<int32_t> start(nl + 1, 0);
+    for (int l = 0; l < nl; ++l) start[l + 1] = start[l] + tval[ti][l];
+    std::vector<int32_t> fill(start.begin(), start.end() - 1);
+    std::vector<uint16_t> inc((size_t)d.n_elem * nc);
+    std::vector<uint16_t> li((size_t)d.n_elem * nc);
+    for (int i = 0; i < d.n_elem; ++i) {
+      const int32_t e = order[tbeg[ti] + i];
+      t.slot_of_elem[e] = d.slot_off + i;
+      t.elem_of_slot[d.slot_off + i] = e;
+      for (int c = 0; c < nc; ++c) {
+        const int32_t g = elems[(int64_t)e * nc + c];
+        li[(size_t)i * nc + c] = (uint16_t)local_of_sorted[std::lower_bound(v.begin(), v.end(), g) - v.begin()];
+      }
+      uint32_t w0 = li[(size_t)i * nc + 0] | ((uint32_t)li[(size_t)i * nc + 1] << 16);
+      uint32_t w1 = li[(size_t)i * nc + 2] | ((uint32_t)(nc == 4 ? li[(size_t)i * nc + 3] : 0) << 16);
+      t.lidx[(size_t)(d.slot_off + i) * 2 + 0] = w0;
+      t.lidx[(size_t)(d.slot_off + i) * 2 + 1] = w1;
+    }
+    for (int c = 0; c < nc; ++c)
+      for (int i = 0; i < d.n_elem; ++i) {
+        const int l = li[(size_t)i * nc + c];
+        inc[fill[l]++] = (uint16_t)(i | (c << 12));
+      }
+    // jagged-diagonal layout: round k holds entry k of every vertex with valence > k
+    int64_t off = d.jds_off;
+    for (int k = 0; k < d.n_rounds; ++k) {
+      int cnt = 0;
+      while (cnt < nl && tval[ti][cnt] > k) ++cnt;
+      t.rounds[(size_t)d.rounds_off + k] = (uint32_t)cnt;
+      for (int l = 0; l < cnt; ++l) t.jds[off + l] = inc[start[l] + k];
+      off += cnt;
+    }
+  }
+  return std::string();
+}
+
+}  // namespace femb

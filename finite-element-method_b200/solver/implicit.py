@@ -1,0 +1,16 @@
+# coding=utf-8
+"""implicit_solver_neo_hookean(obj) and advect_implicit(obj, circle_blocks)
+(reference solver/implicit.py:201-223, 407-437), matrix-free on the GPU.  The dense
+Nv x Nv matrix_A / matrix_AT / matrix_ATA fields of the reference are never formed."""
+import constants
+
+
+def implicit_solver_neo_hookean(obj):
+    it, resid = obj._h.implicit_solve(constants.delta_time, constants.implicit_method,
+                                      1 if constants.preconditioned == 1 else 0)
+    obj.last_solve = {"iters": it, "resid": resid}
+
+
+def advect_implicit(obj, circle_blocks):
+    obj._sync_blocks(circle_blocks)
+    obj._h.advect_implicit(constants.delta_time, constants.g_dir)

@@ -1,0 +1,149 @@
+/* femb200.h -- C ABI of libfemb200.so, the B200-native Neo-Hookean FEM hot path.
+ *
+ * The reference (Jukgei/Finite-Element-Method) has NO FFI layer: its boundary
+ * is Python calling Taichi @ti.kernel functions that mutate Taichi fields
+ * (main.py:101-113).  Each entry point below replaces one of those kernels /
+ * field operations; the citation names the reference interface it stands in
+ * for.  Plain C types only: pointers, sizes, scalars.  Host pointers are
+ * borrowed for the duration of the call.  All device memory is owned by the
+ * library behind the opaque handle.
+ *
+ * Every function returns 0 on success or a negative femb_status; the message
+ * is available from femb_last_error() (thread-local).  There is no CPU
+ * fallback: without a CUDA device object creation fails with FEMB_E_CUDA.
+ *
+ * Calls enqueue work on the object's stream and return; femb_get / femb_sync
+ * synchronise.  A handle is not thread-safe.
+ */
+#ifndef FEMB200_H
+#define FEMB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct femb_object femb_object; /* one soft body: object.py:41-93 `Object` */
+typedef struct femb_tiling femb_tiling; /* host-only view of the element tiling (tests, tools) */
+
+typedef enum femb_status {
+  FEMB_OK = 0,
+  FEMB_E_ARG = -1,   /* bad argument / bad mesh */
+  FEMB_E_CUDA = -2,  /* CUDA runtime error, or no device */
+  FEMB_E_STATE = -3, /* call not valid for this object (e.g. implicit buffers not allocated) */
+  FEMB_E_LIMIT = -4  /* mesh exceeds a tiling limit */
+} femb_status;
+
+/* Field ids for femb_get / femb_set.  Vertex fields are [n_vert*dim] float32 in
+ * the caller's ORIGINAL vertex order; element fields are in original element
+ * order.  (The library renumbers both internally.) */
+typedef enum femb_field {
+  FEMB_F_POS = 0,      /* particles.pos            object.py:13  */
+  FEMB_F_VEL = 1,      /* particles.vel            object.py:14  */
+  FEMB_F_VEL_G = 2,    /* particles.vel_g          object.py:15  */
+  FEMB_F_FORCE = 3,    /* particles.force (= +dE/dx) object.py:19, explicit.py:42-49 */
+  FEMB_F_GRAD = 4,     /* particles.pos.grad       object.py:59 (needs_grad), main.py:107 */
+  FEMB_F_MASS = 5,     /* particles.mass  [n_vert] object.py:18,360 */
+  FEMB_F_REF_POS = 6,  /* particles.ref_pos        object.py:20,342 */
+  FEMB_F_VEC_B = 7,    /* obj.vec_b                object.py:83  */
+  FEMB_F_VEC_X = 8,    /* obj.vec_x                object.py:84  */
+  FEMB_F_PAST_X = 9,   /* obj.past_vec_x           object.py:85  */
+  FEMB_F_DIAG_A = 10,  /* diagonal of matrix_A (matrix-free; implicit.py:399) */
+  FEMB_F_ELEM_VOLUME = 32, /* elements.volume [n_elem]          object.py:34,356 */
+  FEMB_F_ELEM_REF = 33,    /* elements.ref = Dm^-1 [n_elem*dim*dim] row-major, object.py:35,362 */
+  FEMB_F_ELEM_PHI = 34,    /* obj.phi [n_elem] (sized by elements; fixes object.py:68) */
+  FEMB_F_ELEM_H = 35       /* per-element block H_e [n_elem*dim*dim] (implicit.py:141-147) */
+} femb_field;
+
+typedef struct femb_desc {
+  int32_t dim;          /* 2 (triangles) or 3 (tets)      constants.dim, utils.py:10 */
+  int32_t n_vert;
+  int32_t n_elem;
+  const float *verts;   /* [n_vert*dim] raw vertices (object.py:62 ti_vertices) */
+  const int32_t *elems; /* [n_elem*(dim+1)] (object.py:66-67 ti_element) */
+  float center[3];      /* offset added to every vertex, object.py:341 */
+  float rho;            /* object.py:45 */
+  float mu, lambda;     /* object.py:48 */
+  float damping;        /* object.py:50 */
+  int32_t implicit;     /* !=0: allocate the implicit-solver vectors, object.py:78-93 */
+  int32_t tile_elems;   /* elements per tile (<=4096); 0 = library default */
+  int32_t device;       /* CUDA device ordinal; -1 = current device */
+} femb_desc;
+
+typedef struct femb_info {
+  int32_t dim, n_vert, n_elem;
+  int32_t n_tiles, tile_elems, max_tile_verts, max_rounds;
+  int32_t n_interior, n_boundary, n_partials;
+  int32_t smem_bytes, block_threads;
+  int64_t device_bytes; /* total device memory owned by the object */
+} femb_info;
+
+/* ---- lifetime: Object.__init__ + particles_init + elements_init (object.py:44-93,337-362) */
+int femb_object_create(const femb_desc *desc, femb_object **out);
+int femb_object_destroy(femb_object *obj);
+int femb_object_info(const femb_object *obj, femb_info *out);
+/* Run subsequent work on a caller-provided cudaStream_t (e.g. torch's current stream). */
+int femb_set_stream(femb_object *obj, void *cuda_stream);
+
+/* ---- CircleBlocks (circle_blocks.py:15-25): centers [n*dim], radii [n]; radius<=0 disables */
+int femb_blocks_set(femb_object *obj, int32_t n, const float *centers, const float *radii);
+
+/* ---- explicit path */
+/* neo_hookean_1_grad(obj), explicit.py:8-49: force += dE/dx */
+int femb_explicit_grad(femb_object *obj);
+/* compute_energy(obj) under ti.ad.Tape, explicit_auto_diff.py:8-30 + main.py:107-108:
+ * phi[e], U, and pos.grad = dU/dx (overwritten).  U_out may be NULL (no sync). */
+int femb_energy_grad(femb_object *obj, float *U_out);
+/* kinematic(obj, circle_blocks), kinematic.py:9-45.  use_grad!=0 reads pos.grad
+ * (auto_diff==1) and leaves it; otherwise reads force and zeroes it. */
+int femb_kinematic(femb_object *obj, float dt, const float *g_dir, int32_t use_grad);
+/* n_steps x [neo_hookean_1_grad ; kinematic] (main.py:103-110 with auto_diff==0),
+ * fused so the gradient never round-trips through HBM.  Results equal the
+ * two-call sequence bit for bit. */
+int femb_explicit_step(femb_object *obj, float dt, const float *g_dir, int32_t n_steps);
+
+/* ---- implicit path */
+/* implicit_solver_neo_hookean(obj), implicit.py:201-223, matrix-free.
+ * method: 0 Jacobi (implicit.py:227-262), 1 CG (implicit.py:311-386);
+ * preconditioned: CG on A^T A x = A^T b (implicit.py:289-299).
+ * max_iter<=0 / tol<0 select the reference's constants (500 / 1e-5 for CG,
+ * 20000 / 1e-5 for Jacobi).  Writes vel = x. */
+int femb_implicit_solve(femb_object *obj, float dt, int32_t method, int32_t preconditioned,
+                        int32_t max_iter, float tol, int32_t *iters_out, float *resid_out);
+/* advect_implicit(obj, circle_blocks), implicit.py:407-437 */
+int femb_advect_implicit(femb_object *obj, float dt, const float *g_dir);
+/* Pieces of the solve, exposed for parity tests: assemble H_e, b, diag(A) */
+int femb_implicit_assemble(femb_object *obj, float dt);
+/* out = A in (transpose==0) or A^T in (transpose!=0); host vectors [n_vert*dim] */
+int femb_implicit_apply(femb_object *obj, float dt, int32_t transpose, const float *in, float *out);
+
+/* ---- field access: field.to_numpy() / field.from_numpy() */
+int femb_get(femb_object *obj, int32_t field, void *host, size_t bytes);
+int femb_set(femb_object *obj, int32_t field, const void *host, size_t bytes);
+/* obj.U[None] (object.py:69) */
+int femb_get_energy(femb_object *obj, float *U_out);
+int femb_sync(femb_object *obj);
+
+/* ---- diagnostics */
+const char *femb_last_error(void);
+/* number of CUDA kernels this library has launched in this process */
+uint64_t femb_launch_count(void);
+const char *femb_version(void);
+
+/* ---- host-only tiling (no CUDA calls): used by tests to check the layout invariants */
+int femb_tiling_build(int32_t dim, int32_t n_vert, int32_t n_elem, const float *verts,
+                      const int32_t *elems, int32_t tile_elems, femb_tiling **out);
+int femb_tiling_destroy(femb_tiling *t);
+int femb_tiling_info(const femb_tiling *t, femb_info *out);
+/* what: 0 new_of_old[n_vert], 1 slot_of_elem[n_elem], 2 tile descriptors [n_tiles*12],
+ * 3 local vertex table [sum n_lv * 2], 4 jds entries (uint16), 5 round counts (uint32),
+ * 6 packed local indices [n_slots*2] (uint32), 7 boundary ptr [n_boundary+1].
+ * Returns the element count; copies min(count, cap) elements when out != NULL. */
+int64_t femb_tiling_get(const femb_tiling *t, int32_t what, void *out, int64_t cap);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FEMB200_H */
