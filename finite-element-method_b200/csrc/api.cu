@@ -45,7 +45,7 @@ KinArgs femb_object::kin_args(float dt, const float* g_dir) const {
   return k;
 }
 
-static const int kMaxSmem = 227 * 1024;
+static const int kMaxSmem = 226 * 1024;  // 227 KB per CTA minus the kernels' static shared memory
 
 static int tile_smem_bytes(const Tiling& t) {
   const int stride = (t.max_tile_elems + 31) / 32 * 32;

@@ -16,6 +16,9 @@
 #include "dev.cuh"
 #include "launch.h"
 
+#include <stdexcept>
+#include <string>
+
 namespace femb {
 
 enum GatherMode {
@@ -155,10 +158,14 @@ __global__ void __launch_bounds__(kBoundaryBlock) k_boundary(DevTiling tl, typen
 
 template <int D, class Op>
 inline void run_tile_pass(const char* name, const LaunchCfg& c, const DevTiling& tl, const typename Op::Args& a) {
-  static bool attr_set[64] = {};  // per device: the attribute lives in the device's context
-  if (!attr_set[c.device & 63]) {
-    cudaFuncSetAttribute(k_tile<D, Op>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    attr_set[c.device & 63] = true;
+  static int attr_set[64] = {};  // per device (the attribute lives in the device's context): bytes allowed so far
+  if (c.smem > attr_set[c.device & 63]) {
+    const cudaError_t e = cudaFuncSetAttribute(k_tile<D, Op>, cudaFuncAttributeMaxDynamicSharedMemorySize, c.smem);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      throw std::runtime_error(std::string(name) + ": cannot reserve shared memory: " + cudaGetErrorString(e));
+    }
+    attr_set[c.device & 63] = c.smem;
   }
   k_tile<D, Op><<<tl.n_tiles, Op::BLOCK, c.smem, c.stream>>>(tl, a);
   note_launch(name, c.stream);
