@@ -266,7 +266,8 @@ int femb_explicit_step(femb_object* o, float dt, const float* g_dir, int32_t n_s
     for (int s = 0; s < n_steps; ++s)
       launch_explicit(o->dim, EX_STEP, o->cfg, o->dtl, o->e, o->vs, o->mat, kin, nullptr, nullptr);
   };
-  if (n_steps < 4) {
+  // (the legacy default stream cannot be captured)
+  if (n_steps < 4 || o->stream == nullptr || o->stream == cudaStreamLegacy) {
     run();
   } else {
     StepGraph& g = o->graph;
@@ -297,6 +298,34 @@ int femb_explicit_step(femb_object* o, float dt, const float* g_dir, int32_t n_s
     }
     FEMB_CUDA(cudaGraphLaunch(g.exec, o->stream));
   }
+  FEMB_CATCH
+}
+
+int femb_explicit_step_timed(femb_object* o, float dt, const float* g_dir, int32_t n_steps, float* tile_ms,
+                             float* boundary_ms) {
+  FEMB_TRY
+  if (!o || n_steps <= 0 || !tile_ms || !boundary_ms) throw ArgError("femb_explicit_step_timed: bad argument");
+  FEMB_CUDA(cudaSetDevice(o->device));
+  const KinArgs kin = o->kin_args(dt, g_dir);
+  std::vector<cudaEvent_t> ev((size_t)n_steps * 3);
+  for (auto& e : ev) FEMB_CUDA(cudaEventCreate(&e));
+  LaunchCfg cfg = o->cfg;
+  for (int s = 0; s < n_steps; ++s) {
+    FEMB_CUDA(cudaEventRecord(ev[3 * s], o->stream));
+    cfg.ev_mid = ev[3 * s + 1];
+    launch_explicit(o->dim, EX_STEP, cfg, o->dtl, o->e, o->vs, o->mat, kin, nullptr, nullptr);
+    FEMB_CUDA(cudaEventRecord(ev[3 * s + 2], o->stream));
+  }
+  FEMB_CUDA(cudaStreamSynchronize(o->stream));
+  double t = 0.0, b = 0.0;
+  for (int s = 0; s < n_steps; ++s) {
+    float ms = 0.f;
+    FEMB_CUDA(cudaEventElapsedTime(&ms, ev[3 * s], ev[3 * s + 1])); t += ms;
+    FEMB_CUDA(cudaEventElapsedTime(&ms, ev[3 * s + 1], ev[3 * s + 2])); b += ms;
+  }
+  for (auto& e : ev) cudaEventDestroy(e);
+  *tile_ms = (float)t;
+  *boundary_ms = (float)b;
   FEMB_CATCH
 }
 

@@ -46,6 +46,7 @@ struct LaunchCfg {
   int smem;                // dynamic shared memory of the tile kernels
   int sms;
   int device;
+  cudaEvent_t ev_mid = nullptr;  // if set, recorded between the tile and the boundary kernel of a pass
 };
 
 // setup: Dm^-1, volume -> element planes; lumped mass -> pos.w   (object.py:345-362)

@@ -22,7 +22,7 @@ F_ELEM_VOLUME, F_ELEM_REF, F_ELEM_PHI, F_ELEM_H = 32, 33, 34, 35
 
 EXPORTS = [
     "femb_object_create", "femb_object_destroy", "femb_object_info", "femb_set_stream", "femb_blocks_set",
-    "femb_explicit_grad", "femb_energy_grad", "femb_kinematic", "femb_explicit_step", "femb_implicit_solve",
+    "femb_explicit_grad", "femb_energy_grad", "femb_kinematic", "femb_explicit_step", "femb_explicit_step_timed", "femb_implicit_solve",
     "femb_advect_implicit", "femb_implicit_assemble", "femb_implicit_apply", "femb_get", "femb_set",
     "femb_get_energy", "femb_sync", "femb_last_error", "femb_launch_count", "femb_version",
     "femb_tiling_build", "femb_tiling_destroy", "femb_tiling_info", "femb_tiling_get",
@@ -78,6 +78,7 @@ def lib():
         "femb_energy_grad": (C.c_int, [vp, fp]),
         "femb_kinematic": (C.c_int, [vp, f32, fp, i32]),
         "femb_explicit_step": (C.c_int, [vp, f32, fp, i32]),
+        "femb_explicit_step_timed": (C.c_int, [vp, f32, fp, i32, fp, fp]),
         "femb_implicit_solve": (C.c_int, [vp, f32, i32, i32, i32, f32, ip, fp]),
         "femb_advect_implicit": (C.c_int, [vp, f32, fp]),
         "femb_implicit_assemble": (C.c_int, [vp, f32]),
@@ -124,7 +125,10 @@ def gvec(g_dir, dim):
 class Handle:
     """Owns one femb_object."""
 
-    def __init__(self, verts, elems, center, rho, mu, lam, damping, implicit=False, tile_elems=0, device=-1):
+    def __init__(self, verts, elems, center, rho, mu, lam, damping, implicit=False, tile_elems=0, device=-1,
+                 halo_verts=None):
+        if halo_verts is not None:
+            raise NotImplementedError("halo vertices: multi-GPU slabs are not wired up yet")
         verts = np.ascontiguousarray(verts, dtype=np.float32)
         elems = np.ascontiguousarray(elems, dtype=np.int32)
         self.dim = int(verts.shape[1])
@@ -211,6 +215,12 @@ class Handle:
     def explicit_step(self, dt, g_dir, n_steps=1):
         g = gvec(g_dir, self.dim)
         check(lib().femb_explicit_step(self._h, float(dt), _fptr(g), int(n_steps)))
+
+    def explicit_step_timed(self, dt, g_dir, n_steps):
+        g = gvec(g_dir, self.dim)
+        t, b = C.c_float(), C.c_float()
+        check(lib().femb_explicit_step_timed(self._h, float(dt), _fptr(g), int(n_steps), C.byref(t), C.byref(b)))
+        return t.value, b.value
 
     def implicit_solve(self, dt, method, preconditioned, max_iter=0, tol=-1.0, fetch=True):
         if fetch:

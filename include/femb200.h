@@ -103,6 +103,11 @@ int femb_kinematic(femb_object *obj, float dt, const float *g_dir, int32_t use_g
  * fused so the gradient never round-trips through HBM.  Results equal the
  * two-call sequence bit for bit. */
 int femb_explicit_step(femb_object *obj, float dt, const float *g_dir, int32_t n_steps);
+/* Same n_steps fused steps, launched one by one with CUDA events around each kernel:
+ * returns the summed device time (ms) of the tile kernel and of the boundary kernel.
+ * Measurement aid for bench.py's per-kernel roofline; synchronises. */
+int femb_explicit_step_timed(femb_object *obj, float dt, const float *g_dir, int32_t n_steps,
+                             float *tile_ms, float *boundary_ms);
 
 /* ---- implicit path */
 /* implicit_solver_neo_hookean(obj), implicit.py:201-223, matrix-free.
