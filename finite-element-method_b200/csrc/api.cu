@@ -49,7 +49,7 @@ static const int kMaxSmem = 226 * 1024;  // 227 KB per CTA minus the kernels' st
 
 static int tile_smem_bytes(const Tiling& t) {
   const int stride = (t.max_tile_elems + 31) / 32 * 32;
-  return t.max_lv * (int)sizeof(float4) + t.dim * t.dim * stride * (int)sizeof(float);
+  return tile_smem_layout(t.max_lv, (t.max_rounds + 3) / 4 * 4, t.nc, stride, t.dim * t.dim).total;
 }
 
 extern "C" {
@@ -115,8 +115,11 @@ int femb_object_create(const femb_desc* d, femb_object** out) {
     upload(o->d_lidx, t.lidx);
     upload(o->d_new_of_old, t.new_of_old);
     upload(o->d_slot_of_elem, t.slot_of_elem);
+    // CTAs of the tile kernels resident at once = how far ahead the L2 prefetch looks
+    const int occ = std::max(1, std::min(2048 / 256, (227 * 1024) / (tile_smem_bytes(t) + 1024)));
     o->dtl = DevTiling{d_tiles, d_lv, d_jds, d_rounds, d_bptr, t.n_tiles, t.n_interior, t.n_boundary, t.n_vert,
-                       t.n_slots, (t.max_tile_elems + 31) / 32 * 32, t.max_lv};
+                       t.n_slots, (t.max_tile_elems + 31) / 32 * 32, t.max_lv, (t.max_rounds + 3) / 4 * 4, t.nc,
+                       prop.multiProcessorCount * occ};
 
     const size_t ns = (size_t)t.n_slots, nv = (size_t)t.n_vert;
     o->e.p0 = o->alloc<float4>(ns);

@@ -17,7 +17,31 @@ struct DevTiling {
   int n_tiles, n_interior, n_boundary, n_vert, n_slots;
   int stage_stride;      // floats per staging plane (>= max tile elems, multiple of 32)
   int max_lv;
+  int max_rounds;
+  int nc;                // corners per element (dim + 1)
+  int prefetch_dist;     // tiles ahead whose element planes are prefetched into L2 (0 = off)
 };
+
+// Shared-memory layout of k_tile (byte offsets; every region is 16-byte aligned):
+//   sv      [max_lv] float4        staged vertex values
+//   lvt     [max_lv] LocalVert     bulk-copied local-vertex table
+//   rounds  [max_rounds] uint32    bulk-copied JDS round counts
+//   jds     [nc*stage_stride] u16  bulk-copied JDS entries
+//   stage   [n_planes][stage_stride] float
+struct TileSmem {
+  int lvt, rounds, jds, stage, total;
+};
+__host__ __device__ inline TileSmem tile_smem_layout(int max_lv, int max_rounds, int nc, int stage_stride,
+                                                     int n_planes) {
+  TileSmem s;
+  int off = max_lv * 16;
+  s.lvt = off;    off += (max_lv * 8 + 15) / 16 * 16;
+  s.rounds = off; off += (max_rounds * 4 + 15) / 16 * 16;
+  s.jds = off;    off += (nc * stage_stride * 2 + 15) / 16 * 16;
+  s.stage = off;  off += n_planes * stage_stride * 4;
+  s.total = off;
+  return s;
+}
 
 // Element planes, one float4 per slot per plane.
 //   3D  e0 = {idx01, idx23, V,   r00}  e1 = {r01, r02, r10, r11}  e2 = {r12, r20, r21, r22}

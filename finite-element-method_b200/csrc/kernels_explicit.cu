@@ -78,8 +78,17 @@ struct OpSetup {
   __device__ static double* red_buf(const Args&) { return nullptr; }
   __device__ static float4 load_vertex(const Args& a, int gid) { return a.vs.pos[gid]; }
 
-  __device__ static void element(const Args& a, int slot, const float4* sv, float (&out)[NSTAGE], float&) {
-    const uint32_t w0 = a.lidx[2 * slot], w1 = a.lidx[2 * slot + 1];
+  struct Elem {
+    uint32_t w0, w1;
+  };
+  __device__ static void prefetch(const Args&, int, uint32_t) {}
+  __device__ static void load(const Args& a, int slot, Elem& d) {
+    d.w0 = a.lidx[2 * slot];
+    d.w1 = a.lidx[2 * slot + 1];
+  }
+  __device__ static void compute(const Args& a, int slot, const Elem& d, const float4* sv, float (&out)[NSTAGE],
+                                 float&) {
+    const uint32_t w0 = d.w0, w1 = d.w1;
     Mat<D> r;
     edge_matrix<D>(sv, w0, w1, r);  // plain subtractions: nothing to contract
     float vol;
@@ -154,11 +163,12 @@ struct OpExplicit {
   __device__ static double* red_buf(const Args& a) { return a.red; }
   __device__ static float4 load_vertex(const Args& a, int gid) { return a.vs.pos[gid]; }
 
-  __device__ static void element(const Args& a, int slot, const float4* sv, float (&out)[NSTAGE], float& red) {
-    const float4 e0 = a.e.p0[slot];
-    const float4 e1 = a.e.p1[slot];
-    float4 e2 = make_float4(0.f, 0.f, 0.f, 0.f);
-    if constexpr (D == 3) e2 = a.e.p2[slot];
+  using Elem = PlaneElem;
+  __device__ static void prefetch(const Args& a, int slot, uint32_t bytes) { prefetch_planes(a.e, slot, bytes, D == 3); }
+  __device__ static void load(const Args& a, int slot, Elem& d) { load_planes<D>(a.e, slot, d); }
+  __device__ static void compute(const Args& a, int slot, const Elem& d, const float4* sv, float (&out)[NSTAGE],
+                                 float& red) {
+    const float4 e0 = d.a, e1 = d.b, e2 = d.c;
     Mat<D> R, X, F, C;
     unpack_ref<D>(e0, e1, e2, R);
     edge_matrix<D>(sv, __float_as_uint(e0.x), __float_as_uint(e0.y), X);  // explicit.py:11-16

@@ -32,11 +32,12 @@ struct OpAssemble {
   __device__ static double* red_buf(const Args&) { return nullptr; }
   __device__ static float4 load_vertex(const Args& a, int gid) { return a.vs.pos[gid]; }
 
-  __device__ static void element(const Args& a, int slot, const float4* sv, float (&out)[NSTAGE], float&) {
-    const float4 e0 = a.e.p0[slot];
-    const float4 e1 = a.e.p1[slot];
-    float4 e2 = make_float4(0.f, 0.f, 0.f, 0.f);
-    if constexpr (D == 3) e2 = a.e.p2[slot];
+  using Elem = PlaneElem;
+  __device__ static void prefetch(const Args& a, int slot, uint32_t bytes) { prefetch_planes(a.e, slot, bytes, D == 3); }
+  __device__ static void load(const Args& a, int slot, Elem& d) { load_planes<D>(a.e, slot, d); }
+  __device__ static void compute(const Args& a, int slot, const Elem& d, const float4* sv, float (&out)[NSTAGE],
+                                 float&) {
+    const float4 e0 = d.a, e1 = d.b, e2 = d.c;
     Mat<D> R, X, F, C, FiT, Fi;
     unpack_ref<D>(e0, e1, e2, R);
     edge_matrix<D>(sv, __float_as_uint(e0.x), __float_as_uint(e0.y), X);
@@ -120,10 +121,13 @@ struct OpDiag {
   __device__ static float4* partial_buf(const Args& a) { return a.vs.partial; }
   __device__ static double* red_buf(const Args&) { return nullptr; }
   __device__ static float4 load_vertex(const Args& a, int gid) { return a.vs.pos[gid]; }
-  __device__ static void element(const Args& a, int slot, const float4*, float (&out)[NSTAGE], float&) {
-    const float4 h0 = a.h.p0[slot], h1 = a.h.p1[slot];
+  using Elem = PlaneElem;
+  __device__ static void prefetch(const Args& a, int slot, uint32_t bytes) { prefetch_planes(a.h, slot, bytes, D == 3); }
+  __device__ static void load(const Args& a, int slot, Elem& d) { load_planes<D>(a.h, slot, d); }
+  __device__ static void compute(const Args&, int, const Elem& d, const float4*, float (&out)[NSTAGE], float&) {
+    const float4 h0 = d.a, h1 = d.b;
     if constexpr (D == 3) {
-      out[0] = h0.z; out[1] = h1.z; out[2] = a.h.p2[slot].z;
+      out[0] = h0.z; out[1] = h1.z; out[2] = d.c.z;
     } else {
       out[0] = h0.z; out[1] = h1.y;
     }
@@ -166,11 +170,11 @@ struct OpApply {
     }
     return d;
   }
-  __device__ static void element(const Args& a, int slot, const float4* sv, float (&out)[NSTAGE], float&) {
-    const float4 h0 = a.h.p0[slot];
-    const float4 h1 = a.h.p1[slot];
-    float4 h2 = make_float4(0.f, 0.f, 0.f, 0.f);
-    if constexpr (D == 3) h2 = a.h.p2[slot];
+  using Elem = PlaneElem;
+  __device__ static void prefetch(const Args& a, int slot, uint32_t bytes) { prefetch_planes(a.h, slot, bytes, D == 3); }
+  __device__ static void load(const Args& a, int slot, Elem& d) { load_planes<D>(a.h, slot, d); }
+  __device__ static void compute(const Args&, int, const Elem& d, const float4* sv, float (&out)[NSTAGE], float&) {
+    const float4 h0 = d.a, h1 = d.b, h2 = d.c;
     Mat<D> H, E;
     unpack_h<D>(h0, h1, h2, H);
     edge_matrix<D>(sv, __float_as_uint(h0.x), __float_as_uint(h0.y), E);   // e_j = d_{v_j} - d_{v_0}

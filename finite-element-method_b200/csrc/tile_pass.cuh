@@ -1,10 +1,13 @@
 // tile_pass.cuh -- the one kernel skeleton every element-parallel operation uses.
 //
 // k_tile<D, Op>:   one CTA per tile
-//   1. stage the tile's vertices (Op::load_vertex) in shared memory,
-//   2. every thread computes Op::element for its elements and stages the
-//      per-element contribution matrix in shared memory (plane-major, so the
-//      stores are conflict-free),
+//   0. one thread issues TMA bulk copies of the tile's lists (local-vertex table,
+//      JDS round counts, JDS entries) into shared memory and an L2 prefetch of
+//      the element planes of the tile that will run on this SM slot next,
+//   1. the tile's vertices (Op::load_vertex) are staged in shared memory,
+//   2. every thread computes its elements (loads front-batched two elements deep)
+//      and stages the per-element contribution matrix in shared memory
+//      (plane-major: conflict-free stores),
 //   3. every thread gathers the contributions of one local vertex through the
 //      tile's jagged-diagonal incidence list in a FIXED order (deterministic --
 //      no float atomics), then either finishes the vertex (Op::vertex, interior
@@ -15,6 +18,7 @@
 #pragma once
 #include "dev.cuh"
 #include "launch.h"
+#include "tma.cuh"
 
 #include <stdexcept>
 #include <string>
@@ -23,7 +27,7 @@ namespace femb {
 
 enum GatherMode {
   G_STAR = 0,     // corner j>=1 gets column j-1 of the staged D x D matrix, corner 0 gets -(sum of columns)
-  G_UNIFORM = 1   // every corner gets the staged D-vector, corner 0 weighted by Op::w0()
+  G_UNIFORM = 1   // every corner gets the staged vector, corner 0 weighted by Op::w0()
 };
 
 __device__ __forceinline__ float warp_sum(float v) {
@@ -48,19 +52,31 @@ __device__ __forceinline__ float block_sum(float v, float* s_warp) {
   return r;
 }
 
+// the three float4 of one element slot, loaded with streaming (no L1 allocate) loads
+struct PlaneElem {
+  float4 a, b, c;
+};
+
+template <int D>
+__device__ __forceinline__ void load_planes(const Planes& p, int slot, PlaneElem& d) {
+  d.a = __ldcs(p.p0 + slot);
+  d.b = __ldcs(p.p1 + slot);
+  if constexpr (D == 3) d.c = __ldcs(p.p2 + slot);
+  else d.c = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+
 template <int D, int MODE, int NV>
-__device__ __forceinline__ void gather_local_vertex(const DevTiling& tl, const TileDesc& td, const float* stage,
+__device__ __forceinline__ void gather_local_vertex(int S, int n_rounds, const uint32_t* __restrict__ rounds,
+                                                    const uint16_t* __restrict__ jds, const float* __restrict__ stage,
                                                     int l, float w0, float (&acc)[D]) {
-  const int S = tl.stage_stride;
 #pragma unroll
   for (int i = 0; i < D; ++i) acc[i] = 0.f;
-  const uint16_t* jds = tl.jds + td.jds_off;
-  const uint32_t* rounds = tl.rounds + td.rounds_off;
-  int off = 0;
-  for (int k = 0; k < td.n_rounds; ++k) {
+  int off = l;
+  for (int k = 0; k < n_rounds; ++k) {
     const int cnt = (int)rounds[k];
     if (l >= cnt) break;  // valences are sorted descending: no later round includes l
-    const uint32_t ent = jds[off + l];
+    const uint32_t ent = jds[off];
+    off += cnt;
     const int e = ent & 0xfffu;
     const int c = ent >> 12;
     if (MODE == G_STAR) {
@@ -82,7 +98,6 @@ __device__ __forceinline__ void gather_local_vertex(const DevTiling& tl, const T
 #pragma unroll
       for (int i = 0; i < NV; ++i) acc[i] += w * stage[i * S + e];
     }
-    off += cnt;
   }
 }
 
@@ -90,29 +105,71 @@ template <int D, class Op>
 __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile(DevTiling tl, typename Op::Args a) {
   extern __shared__ float4 smem4[];
   __shared__ float s_warp[32];
+  __shared__ uint64_t s_bar[2];   // [0]: local-vertex table landed, [1]: JDS lists landed
   if (Op::early_exit(a)) return;
-  float4* sv = smem4;
-  float* stage = reinterpret_cast<float*>(smem4 + tl.max_lv);
   const TileDesc td = tl.tiles[blockIdx.x];
   const int S = tl.stage_stride;
-  const LocalVert* lvt = tl.lv + td.lv_off;
+  const TileSmem lay = tile_smem_layout(tl.max_lv, tl.max_rounds, tl.nc, S, Op::NSTAGE);
+  char* smem = reinterpret_cast<char*>(smem4);
+  float4* sv = smem4;
+  LocalVert* s_lv = reinterpret_cast<LocalVert*>(smem + lay.lvt);
+  uint32_t* s_rounds = reinterpret_cast<uint32_t*>(smem + lay.rounds);
+  uint16_t* s_jds = reinterpret_cast<uint16_t*>(smem + lay.jds);
+  float* stage = reinterpret_cast<float*>(smem + lay.stage);
 
-  for (int l = threadIdx.x; l < td.n_lv; l += blockDim.x) sv[l] = Op::load_vertex(a, lvt[l].gid);
+  if (threadIdx.x == 0) {
+    mbar_init(&s_bar[0], 1);
+    mbar_init(&s_bar[1], 1);
+    mbar_fence_init();
+    const uint32_t lv_bytes = (uint32_t)round_up(td.n_lv * 8, 16);
+    const uint32_t r_bytes = (uint32_t)round_up(td.n_rounds * 4, 16);
+    const uint32_t j_bytes = (uint32_t)round_up(td.n_elem * tl.nc * 2, 16);
+    mbar_expect_tx(&s_bar[0], lv_bytes);
+    bulk_g2s(s_lv, tl.lv + td.lv_off, lv_bytes, &s_bar[0]);
+    mbar_expect_tx(&s_bar[1], r_bytes + j_bytes);
+    bulk_g2s(s_rounds, tl.rounds + td.rounds_off, r_bytes, &s_bar[1]);
+    bulk_g2s(s_jds, tl.jds + td.jds_off, j_bytes, &s_bar[1]);
+    // L2 prefetch of the tile that will occupy this SM slot after us
+    const int nxt = blockIdx.x + tl.prefetch_dist;
+    if (tl.prefetch_dist > 0 && nxt < tl.n_tiles) {
+      const TileDesc tn = tl.tiles[nxt];
+      Op::prefetch(a, tn.slot_off, (uint32_t)(round_up(tn.n_elem, 32) * 16));
+    }
+  }
+  __syncthreads();          // barrier words initialised before anyone polls them
+  mbar_wait(&s_bar[0], 0);
+
+  for (int l = threadIdx.x; l < td.n_lv; l += blockDim.x) sv[l] = Op::load_vertex(a, s_lv[l].gid);
   __syncthreads();
 
   float red = 0.f;
-  for (int e = threadIdx.x; e < td.n_elem; e += blockDim.x) {
-    float out[Op::NSTAGE];
-    Op::element(a, td.slot_off + e, sv, out, red);
+  const int B = blockDim.x;
+  for (int e = threadIdx.x; e < td.n_elem; e += 2 * B) {
+    typename Op::Elem d0, d1;
+    const bool two = e + B < td.n_elem;
+    Op::load(a, td.slot_off + e, d0);
+    if (two) Op::load(a, td.slot_off + e + B, d1);
+    {
+      float out[Op::NSTAGE];
+      Op::compute(a, td.slot_off + e, d0, sv, out, red);
 #pragma unroll
-    for (int k = 0; k < Op::NSTAGE; ++k) stage[k * S + e] = out[k];
+      for (int k = 0; k < Op::NSTAGE; ++k) stage[k * S + e] = out[k];
+    }
+    if (two) {
+      float out[Op::NSTAGE];
+      Op::compute(a, td.slot_off + e + B, d1, sv, out, red);
+#pragma unroll
+      for (int k = 0; k < Op::NSTAGE; ++k) stage[k * S + e + B] = out[k];
+    }
   }
   __syncthreads();
+  mbar_wait(&s_bar[1], 0);
 
   for (int l = threadIdx.x; l < td.n_lv; l += blockDim.x) {
     float acc[D];
-    gather_local_vertex<D, Op::GATHER, (Op::NSTAGE < D ? Op::NSTAGE : D)>(tl, td, stage, l, Op::w0(), acc);
-    const LocalVert v = lvt[l];
+    gather_local_vertex<D, Op::GATHER, (Op::NSTAGE < D ? Op::NSTAGE : D)>(S, td.n_rounds, s_rounds, s_jds, stage, l,
+                                                                         Op::w0(), acc);
+    const LocalVert v = s_lv[l];
     if (v.part < 0) {
       Op::vertex(a, v.gid, sv[l], acc, red);
     } else {
@@ -156,18 +213,26 @@ __global__ void __launch_bounds__(kBoundaryBlock) k_boundary(DevTiling tl, typen
   }
 }
 
+// prefetch helper shared by the Ops: `bytes` per plane starting at slot `slot`
+__device__ __forceinline__ void prefetch_planes(const Planes& p, int slot, uint32_t bytes, bool three) {
+  bulk_prefetch_l2(p.p0 + slot, bytes);
+  bulk_prefetch_l2(p.p1 + slot, bytes);
+  if (three) bulk_prefetch_l2(p.p2 + slot, bytes);
+}
+
 template <int D, class Op>
 inline void run_tile_pass(const char* name, const LaunchCfg& c, const DevTiling& tl, const typename Op::Args& a) {
   static int attr_set[64] = {};  // per device (the attribute lives in the device's context): bytes allowed so far
-  if (c.smem > attr_set[c.device & 63]) {
-    const cudaError_t e = cudaFuncSetAttribute(k_tile<D, Op>, cudaFuncAttributeMaxDynamicSharedMemorySize, c.smem);
+  const int smem = tile_smem_layout(tl.max_lv, tl.max_rounds, tl.nc, tl.stage_stride, Op::NSTAGE).total;
+  if (smem > attr_set[c.device & 63]) {
+    const cudaError_t e = cudaFuncSetAttribute(k_tile<D, Op>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) {
       cudaGetLastError();
       throw std::runtime_error(std::string(name) + ": cannot reserve shared memory: " + cudaGetErrorString(e));
     }
-    attr_set[c.device & 63] = c.smem;
+    attr_set[c.device & 63] = smem;
   }
-  k_tile<D, Op><<<tl.n_tiles, Op::BLOCK, c.smem, c.stream>>>(tl, a);
+  k_tile<D, Op><<<tl.n_tiles, Op::BLOCK, smem, c.stream>>>(tl, a);
   note_launch(name, c.stream);
   if (c.ev_mid) cudaEventRecord(c.ev_mid, c.stream);
   if (tl.n_boundary > 0) {

@@ -173,9 +173,11 @@ std::string build_tiling(int dim, int n_vert, int n_elem, const float* verts,
       TileDesc& d = t.tiles[ti];
       if (d.n_lv > 65535) return "tile has more than 65535 local vertices";
       d.slot_off = (int32_t)slot; slot += (d.n_elem + 31) / 32 * 32;
-      d.lv_off = (int32_t)lvo;   lvo += d.n_lv;
-      d.jds_off = (int32_t)jo;   jo += (int64_t)d.n_elem * nc;
-      d.rounds_off = (int32_t)ro; ro += d.n_rounds;
+      // every per-tile list starts 16-byte aligned and owns a multiple of 16 bytes: the
+      // kernels fetch them with bulk (TMA) copies
+      d.lv_off = (int32_t)lvo;   lvo += (d.n_lv + 1) / 2 * 2;
+      d.jds_off = (int32_t)jo;   jo += ((int64_t)d.n_elem * nc + 7) / 8 * 8;
+      d.rounds_off = (int32_t)ro; ro += (d.n_rounds + 3) / 4 * 4;
       d.int_base = ib;           ib += d.n_int;
       t.max_tile_elems = std::max(t.max_tile_elems, d.n_elem);
       t.max_lv = std::max(t.max_lv, d.n_lv);
