@@ -48,8 +48,7 @@ KinArgs femb_object::kin_args(float dt, const float* g_dir) const {
 static const int kMaxSmem = 226 * 1024;  // 227 KB per CTA minus the kernels' static shared memory
 
 static int tile_smem_bytes(const Tiling& t) {
-  const int stride = (t.max_tile_elems + 31) / 32 * 32;
-  return tile_smem_layout(t.max_lv, (t.max_rounds + 3) / 4 * 4, t.nc, stride, t.dim * t.dim).total;
+  return tile_smem_layout(t.max_lv, (t.max_rounds + 3) / 4 * 4, t.nc, (t.dim + 1) * t.dim).total;
 }
 
 extern "C" {
@@ -84,7 +83,7 @@ int femb_object_create(const femb_desc* d, femb_object** out) {
     for (int v = 0; v < d->n_vert; ++v)
       for (int k = 0; k < dim; ++k) pos[(size_t)v * dim + k] = d->verts[(size_t)v * dim + k] + d->center[k];
 
-    int T = d->tile_elems > 0 ? d->tile_elems : (dim == 3 ? 2304 : 2048);
+    int T = d->tile_elems > 0 ? std::min(d->tile_elems, kStride) : kStride;
     for (;;) {
       const std::string err = build_tiling(dim, d->n_vert, d->n_elem, pos.data(), d->elems, T, o->til);
       if (!err.empty()) throw ArgError(err);
@@ -182,6 +181,7 @@ static void fill_info(const Tiling& t, femb_info* i) {
   i->n_interior = t.n_interior; i->n_boundary = t.n_boundary; i->n_partials = t.n_partials;
   i->smem_bytes = tile_smem_bytes(t);
   i->block_threads = 256;
+  i->stage_stride = kStride;
 }
 
 int femb_object_info(const femb_object* o, femb_info* out) {

@@ -31,14 +31,13 @@ struct DevTiling {
 struct TileSmem {
   int lvt, rounds, jds, stage, total;
 };
-__host__ __device__ inline TileSmem tile_smem_layout(int max_lv, int max_rounds, int nc, int stage_stride,
-                                                     int n_planes) {
+__host__ __device__ inline TileSmem tile_smem_layout(int max_lv, int max_rounds, int nc, int n_planes) {
   TileSmem s;
   int off = max_lv * 16;
   s.lvt = off;    off += (max_lv * 8 + 15) / 16 * 16;
   s.rounds = off; off += (max_rounds * 4 + 15) / 16 * 16;
-  s.jds = off;    off += (nc * stage_stride * 2 + 15) / 16 * 16;
-  s.stage = off;  off += n_planes * stage_stride * 4;
+  s.jds = off;    off += (nc * kStride * 2 + 15) / 16 * 16;
+  s.stage = off;  off += n_planes * kStride * 4;
   s.total = off;
   return s;
 }

@@ -65,36 +65,34 @@ __device__ __forceinline__ void load_planes(const Planes& p, int slot, PlaneElem
   else d.c = make_float4(0.f, 0.f, 0.f, 0.f);
 }
 
+// Number of shared-memory staging planes of an Op: G_STAR ops stage the D x D contribution
+// matrix plus its negated column sum (the share of corner 0), so every incidence reads D
+// consecutive planes at a precomputed offset -- no branch on the corner in the gather.
+template <int D, class Op>
+__host__ __device__ constexpr int n_planes() {
+  return Op::GATHER == G_STAR ? Op::NSTAGE + D : Op::NSTAGE;
+}
+
 template <int D, int MODE, int NV>
-__device__ __forceinline__ void gather_local_vertex(int S, int n_rounds, const uint32_t* __restrict__ rounds,
+__device__ __forceinline__ void gather_local_vertex(int n_rounds, const uint32_t* __restrict__ rounds,
                                                     const uint16_t* __restrict__ jds, const float* __restrict__ stage,
                                                     int l, float w0, float (&acc)[D]) {
+  constexpr int S = kStride;
 #pragma unroll
   for (int i = 0; i < D; ++i) acc[i] = 0.f;
   int off = l;
   for (int k = 0; k < n_rounds; ++k) {
     const int cnt = (int)rounds[k];
     if (l >= cnt) break;  // valences are sorted descending: no later round includes l
-    const uint32_t ent = jds[off];
+    const uint32_t ent = jds[off];   // = jds_entry(D, e, c): word offset of the first plane to read
     off += cnt;
-    const int e = ent & 0xfffu;
-    const int c = ent >> 12;
     if (MODE == G_STAR) {
-      if (c) {
-        const float* s = stage + (c - 1) * D * S + e;
+      const float* s = stage + ent;
 #pragma unroll
-        for (int i = 0; i < D; ++i) acc[i] += s[i * S];
-      } else {
-#pragma unroll
-        for (int i = 0; i < D; ++i) {
-          float t = stage[i * S + e];
-#pragma unroll
-          for (int j = 1; j < D; ++j) t += stage[(j * D + i) * S + e];
-          acc[i] -= t;
-        }
-      }
+      for (int i = 0; i < D; ++i) acc[i] += s[i * S];
     } else {
-      const float w = c ? 1.f : w0;
+      const int e = ent % S;
+      const float w = ent >= (uint32_t)(D * D * S) ? w0 : 1.f;   // corner 0 entries live past plane D*D
 #pragma unroll
       for (int i = 0; i < NV; ++i) acc[i] += w * stage[i * S + e];
     }
@@ -108,8 +106,8 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile(DevTiling tl, 
   __shared__ uint64_t s_bar[2];   // [0]: local-vertex table landed, [1]: JDS lists landed
   if (Op::early_exit(a)) return;
   const TileDesc td = tl.tiles[blockIdx.x];
-  const int S = tl.stage_stride;
-  const TileSmem lay = tile_smem_layout(tl.max_lv, tl.max_rounds, tl.nc, S, Op::NSTAGE);
+  constexpr int S = kStride;
+  const TileSmem lay = tile_smem_layout(tl.max_lv, tl.max_rounds, tl.nc, n_planes<D, Op>());
   char* smem = reinterpret_cast<char*>(smem4);
   float4* sv = smem4;
   LocalVert* s_lv = reinterpret_cast<LocalVert*>(smem + lay.lvt);
@@ -136,38 +134,50 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile(DevTiling tl, 
       Op::prefetch(a, tn.slot_off, (uint32_t)(round_up(tn.n_elem, 32) * 16));
     }
   }
+  const int B = blockDim.x;
+  // element data of the first two elements of this thread: in flight while the vertices are staged
+  typename Op::Elem d0, d1;
+  if ((int)threadIdx.x < td.n_elem) Op::load(a, td.slot_off + threadIdx.x, d0);
+  if ((int)threadIdx.x + B < td.n_elem) Op::load(a, td.slot_off + threadIdx.x + B, d1);
+
   __syncthreads();          // barrier words initialised before anyone polls them
   mbar_wait(&s_bar[0], 0);
 
-  for (int l = threadIdx.x; l < td.n_lv; l += blockDim.x) sv[l] = Op::load_vertex(a, s_lv[l].gid);
+  for (int l = threadIdx.x; l < td.n_lv; l += B) sv[l] = Op::load_vertex(a, s_lv[l].gid);
   __syncthreads();
 
   float red = 0.f;
-  const int B = blockDim.x;
+  auto one = [&](int e, const typename Op::Elem& d) {
+    float out[Op::NSTAGE];
+    Op::compute(a, td.slot_off + e, d, sv, out, red);
+    float* s = stage + e;
+#pragma unroll
+    for (int k = 0; k < Op::NSTAGE; ++k) s[k * S] = out[k];
+    if (Op::GATHER == G_STAR) {   // share of corner 0: f0 = -(sum of columns)   (explicit.py:42-49)
+#pragma unroll
+      for (int i = 0; i < D; ++i) {
+        float t = out[i];
+#pragma unroll
+        for (int j = 1; j < D; ++j) t += out[j * D + i];
+        s[(D * D + i) * S] = -t;
+      }
+    }
+  };
   for (int e = threadIdx.x; e < td.n_elem; e += 2 * B) {
-    typename Op::Elem d0, d1;
     const bool two = e + B < td.n_elem;
-    Op::load(a, td.slot_off + e, d0);
-    if (two) Op::load(a, td.slot_off + e + B, d1);
-    {
-      float out[Op::NSTAGE];
-      Op::compute(a, td.slot_off + e, d0, sv, out, red);
-#pragma unroll
-      for (int k = 0; k < Op::NSTAGE; ++k) stage[k * S + e] = out[k];
+    if (e != (int)threadIdx.x) {
+      Op::load(a, td.slot_off + e, d0);
+      if (two) Op::load(a, td.slot_off + e + B, d1);
     }
-    if (two) {
-      float out[Op::NSTAGE];
-      Op::compute(a, td.slot_off + e + B, d1, sv, out, red);
-#pragma unroll
-      for (int k = 0; k < Op::NSTAGE; ++k) stage[k * S + e + B] = out[k];
-    }
+    one(e, d0);
+    if (two) one(e + B, d1);
   }
   __syncthreads();
   mbar_wait(&s_bar[1], 0);
 
-  for (int l = threadIdx.x; l < td.n_lv; l += blockDim.x) {
+  for (int l = threadIdx.x; l < td.n_lv; l += B) {
     float acc[D];
-    gather_local_vertex<D, Op::GATHER, (Op::NSTAGE < D ? Op::NSTAGE : D)>(S, td.n_rounds, s_rounds, s_jds, stage, l,
+    gather_local_vertex<D, Op::GATHER, (Op::NSTAGE < D ? Op::NSTAGE : D)>(td.n_rounds, s_rounds, s_jds, stage, l,
                                                                          Op::w0(), acc);
     const LocalVert v = s_lv[l];
     if (v.part < 0) {
@@ -223,7 +233,7 @@ __device__ __forceinline__ void prefetch_planes(const Planes& p, int slot, uint3
 template <int D, class Op>
 inline void run_tile_pass(const char* name, const LaunchCfg& c, const DevTiling& tl, const typename Op::Args& a) {
   static int attr_set[64] = {};  // per device (the attribute lives in the device's context): bytes allowed so far
-  const int smem = tile_smem_layout(tl.max_lv, tl.max_rounds, tl.nc, tl.stage_stride, Op::NSTAGE).total;
+  const int smem = tile_smem_layout(tl.max_lv, tl.max_rounds, tl.nc, n_planes<D, Op>()).total;
   if (smem > attr_set[c.device & 63]) {
     const cudaError_t e = cudaFuncSetAttribute(k_tile<D, Op>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) {

@@ -74,7 +74,7 @@ std::string build_tiling(int dim, int n_vert, int n_elem, const float* verts,
   if (dim != 2 && dim != 3) return "dim must be 2 or 3";
   if (n_vert <= 0 || n_elem <= 0) return "empty mesh";
   if (!verts || !elems) return "null mesh arrays";
-  if (tile_elems < 32 || tile_elems > 4096) return "tile_elems must be in [32, 4096]";
+  if (tile_elems < 32 || tile_elems > kStride) return "tile_elems must be in [32, " + std::to_string(kStride) + "]";
   const int nc = dim + 1;
   for (int64_t i = 0; i < (int64_t)n_elem * nc; ++i)
     if (elems[i] < 0 || elems[i] >= n_vert) return "element index out of range";
@@ -263,7 +263,7 @@ std::string build_tiling(int dim, int n_vert, int n_elem, const float* verts,
     for (int c = 0; c < nc; ++c)
       for (int i = 0; i < d.n_elem; ++i) {
         const int l = li[(size_t)i * nc + c];
-        inc[fill[l]++] = (uint16_t)(i | (c << 12));
+        inc[fill[l]++] = (uint16_t)jds_entry(dim, i, c);
       }
     // jagged-diagonal layout: round k holds entry k of every vertex with valence > k
     int64_t off = d.jds_off;

@@ -18,6 +18,18 @@
 
 namespace femb {
 
+// Capacity of a tile in elements == stride (in floats) of one shared-memory staging plane.
+// Compile-time so that every staging access is base register + immediate offset.
+#ifndef FEMB_TILE_CAP
+#define FEMB_TILE_CAP 1536
+#endif
+constexpr int kStride = FEMB_TILE_CAP;
+
+// JDS entry of (element slot e in tile, corner c): the staging-plane word offset the gather
+// reads first.  Corner j>=1 owns planes (j-1)*dim .. +dim-1 (column j-1 of the element's
+// contribution matrix), corner 0 owns planes dim*dim .. +dim-1 (minus the column sum).
+constexpr int jds_entry(int dim, int e, int c) { return (c == 0 ? dim * dim : (c - 1) * dim) * kStride + e; }
+
 struct TileDesc {       // 12 x int32, mirrored on the device
   int32_t slot_off;     // first element slot of the tile in the element planes
   int32_t n_elem;

@@ -42,7 +42,7 @@ class Desc(C.Structure):
 class Info(C.Structure):
     _fields_ = [(n, C.c_int32) for n in (
         "dim", "n_vert", "n_elem", "n_tiles", "tile_elems", "max_tile_verts", "max_rounds",
-        "n_interior", "n_boundary", "n_partials", "smem_bytes", "block_threads")] + [("device_bytes", C.c_int64)]
+        "n_interior", "n_boundary", "n_partials", "smem_bytes", "block_threads", "stage_stride", "reserved0")] + [("device_bytes", C.c_int64)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

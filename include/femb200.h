@@ -68,7 +68,7 @@ typedef struct femb_desc {
   float mu, lambda;     /* object.py:48 */
   float damping;        /* object.py:50 */
   int32_t implicit;     /* !=0: allocate the implicit-solver vectors, object.py:78-93 */
-  int32_t tile_elems;   /* elements per tile (<=4096); 0 = library default */
+  int32_t tile_elems;   /* elements per tile (<= femb_info.stage_stride); 0 = library default */
   int32_t device;       /* CUDA device ordinal; -1 = current device */
 } femb_desc;
 
@@ -77,6 +77,7 @@ typedef struct femb_info {
   int32_t n_tiles, tile_elems, max_tile_verts, max_rounds;
   int32_t n_interior, n_boundary, n_partials;
   int32_t smem_bytes, block_threads;
+  int32_t stage_stride, reserved0; /* compile-time tile capacity == staging-plane stride (JDS entry encoding) */
   int64_t device_bytes; /* total device memory owned by the object */
 } femb_info;
 

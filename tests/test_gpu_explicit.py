@@ -23,7 +23,7 @@ def capi():
 
 CASES = {
     "cube_multi_tile": lambda: (cube_case(n=8), MAT3, 256),
-    "cube_one_tile": lambda: (cube_case(n=4), MAT3, 4096),
+    "cube_one_tile": lambda: (cube_case(n=4), MAT3, 0),      # 384 tets < default tile capacity
     "box_ragged": lambda: (cube_case(dims=(9, 5, 7), seed=3), MAT3, 320),
     "square_default_json": lambda: (square_case(), MAT2, 0),
     "square_multi_tile": lambda: (square_case(s=24, seed=4), MAT2, 64),

@@ -52,7 +52,11 @@ def _emulate(t, nc, vals):
             assert prev is None or cnt <= prev  # valences sorted descending
             prev = cnt
             ent = jds[off:off + cnt].astype(np.int64)
-            e, c = ent & 0xFFF, ent >> 12
+            # entry = staging-plane word offset: planes (c-1)*dim.. for corner c>=1, dim*dim.. for corner 0
+            S, dim = t.info["stage_stride"], nc - 1
+            e, plane = ent % S, ent // S
+            c = np.where(plane == dim * dim, 0, plane // dim + 1)
+            assert (plane % dim == 0).all()
             assert (e < n_elem).all() and (c < nc).all()
             acc[:cnt] += vals[elem_of_slot[slot_off + e], c]
             off += cnt
@@ -82,7 +86,7 @@ def test_tile_gather_equals_scatter(case):
     else:  # shuffled element order, permuted corners, a single tile
         verts, el = o.kuhn_box(3, 3, 3, 0.1)
         el = el[rng.permutation(len(el))]
-        T = 4096
+        T = 1024
     verts = verts.astype(np.float32)
     nc = el.shape[1]
     t = _capi.HostTiling(verts, el, T)
@@ -130,8 +134,8 @@ def test_tiling_rejects_bad_meshes():
 def test_large_structured_tiling_stats():
     """C3-like spacing at reduced size: tiles are compact (few boundary vertices)."""
     verts, el = o.kuhn_box(24, 24, 24, 0.01)
-    t = _capi.HostTiling(verts.astype(np.float32), el, 2304)
+    t = _capi.HostTiling(verts.astype(np.float32), el, 1536)
     info = t.info
-    assert info["n_tiles"] >= len(el) // 2304
+    assert info["n_tiles"] >= len(el) // 1536 and info["stage_stride"] >= 1536
     assert info["max_rounds"] == 24            # interior Kuhn valence
     assert info["n_boundary"] < 0.75 * len(verts)
