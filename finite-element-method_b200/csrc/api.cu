@@ -115,7 +115,7 @@ int femb_object_create(const femb_desc* d, femb_object** out) {
     upload(o->d_new_of_old, t.new_of_old);
     upload(o->d_slot_of_elem, t.slot_of_elem);
     // CTAs of the tile kernels resident at once = how far ahead the L2 prefetch looks
-    const int occ = std::max(1, std::min(2048 / 256, (227 * 1024) / (tile_smem_bytes(t) + 1024)));
+    const int occ = std::max(1, std::min(2048 / kBlock, (227 * 1024) / (tile_smem_bytes(t) + 1024)));
     o->dtl = DevTiling{d_tiles, d_lv, d_jds, d_rounds, d_bptr, t.n_tiles, t.n_interior, t.n_boundary, t.n_vert,
                        t.n_slots, (t.max_tile_elems + 31) / 32 * 32, t.max_lv, (t.max_rounds + 3) / 4 * 4, t.nc,
                        prop.multiProcessorCount * occ};
@@ -180,7 +180,7 @@ static void fill_info(const Tiling& t, femb_info* i) {
   i->n_tiles = t.n_tiles; i->tile_elems = t.T; i->max_tile_verts = t.max_lv; i->max_rounds = t.max_rounds;
   i->n_interior = t.n_interior; i->n_boundary = t.n_boundary; i->n_partials = t.n_partials;
   i->smem_bytes = tile_smem_bytes(t);
-  i->block_threads = 256;
+  i->block_threads = kBlock;
   i->stage_stride = kStride;
 }
 

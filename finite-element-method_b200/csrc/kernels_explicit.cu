@@ -64,7 +64,7 @@ __device__ __forceinline__ void kinematic_update(float4& p, float4& v, const flo
 // ---------------------------------------------------------------------------
 template <int D>
 struct OpSetup {
-  static constexpr int BLOCK = 256, MIN_CTAS = 2, NSTAGE = 1, GATHER = G_UNIFORM;
+  static constexpr int BLOCK = kBlock, MIN_CTAS = kMinCtas,NSTAGE = 1, GATHER = G_UNIFORM;
   static constexpr bool REDUCE = false;
   struct Args {
     Planes e;
@@ -147,7 +147,7 @@ struct OpSetup {
 // ---------------------------------------------------------------------------
 template <int D, int MODE>
 struct OpExplicit {
-  static constexpr int BLOCK = 256, MIN_CTAS = 2, NSTAGE = D * D, GATHER = G_STAR;
+  static constexpr int BLOCK = kBlock, MIN_CTAS = kMinCtas,NSTAGE = D * D, GATHER = G_STAR;
   static constexpr bool REDUCE = (MODE == EX_ENERGY);
   struct Args {
     Planes e;

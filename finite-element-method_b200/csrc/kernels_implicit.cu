@@ -17,7 +17,7 @@ namespace femb {
 // ---------------------------------------------------------------------------
 template <int D>
 struct OpAssemble {
-  static constexpr int BLOCK = 256, MIN_CTAS = 2, NSTAGE = D * D, GATHER = G_STAR;
+  static constexpr int BLOCK = kBlock, MIN_CTAS = kMinCtas,NSTAGE = D * D, GATHER = G_STAR;
   static constexpr bool REDUCE = false;
   struct Args {
     Planes e, h;
@@ -108,7 +108,7 @@ struct OpAssemble {
 // diag(A)_{v,k} = 1 - dt^2/m_v sum_e c_{e,v} H_e[k,k]; c = dim at local vertex 0
 template <int D>
 struct OpDiag {
-  static constexpr int BLOCK = 256, MIN_CTAS = 2, NSTAGE = D, GATHER = G_UNIFORM;
+  static constexpr int BLOCK = kBlock, MIN_CTAS = kMinCtas,NSTAGE = D, GATHER = G_UNIFORM;
   static constexpr bool REDUCE = false;
   struct Args {
     Planes h;
@@ -143,7 +143,7 @@ struct OpDiag {
 // ---------------------------------------------------------------------------
 template <int D, int TR>
 struct OpApply {
-  static constexpr int BLOCK = 256, MIN_CTAS = 2, NSTAGE = D * D, GATHER = G_STAR;
+  static constexpr int BLOCK = kBlock, MIN_CTAS = kMinCtas,NSTAGE = D * D, GATHER = G_STAR;
   static constexpr bool REDUCE = true;
   struct Args {
     Planes h;

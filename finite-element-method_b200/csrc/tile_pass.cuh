@@ -81,21 +81,39 @@ __device__ __forceinline__ void gather_local_vertex(int n_rounds, const uint32_t
 #pragma unroll
   for (int i = 0; i < D; ++i) acc[i] = 0.f;
   int off = l;
-  for (int k = 0; k < n_rounds; ++k) {
-    const int cnt = (int)rounds[k];
-    if (l >= cnt) break;  // valences are sorted descending: no later round includes l
-    const uint32_t ent = jds[off];   // = jds_entry(D, e, c): word offset of the first plane to read
-    off += cnt;
-    if (MODE == G_STAR) {
-      const float* s = stage + ent;
+  // Four rounds per trip: the four round counts come in one LDS.128 (the table is padded with
+  // zeros to a multiple of 4), the four entries and their 4*D staged values are independent
+  // loads, and the adds keep the round order -> same sums as the one-round-at-a-time loop.
+  const uint4* rounds4 = reinterpret_cast<const uint4*>(rounds);
+  for (int k = 0; k < n_rounds; k += 4) {
+    const uint4 c4 = rounds4[k >> 2];
+    const int cnt[4] = {(int)c4.x, (int)c4.y, (int)c4.z, (int)c4.w};
+    if (l >= cnt[0]) break;  // valences are sorted descending: no later round includes l
+    uint32_t ent[4];
+    bool on[4];
 #pragma unroll
-      for (int i = 0; i < D; ++i) acc[i] += s[i * S];
-    } else {
-      const int e = ent % S;
-      const float w = ent >= (uint32_t)(D * D * S) ? w0 : 1.f;   // corner 0 entries live past plane D*D
-#pragma unroll
-      for (int i = 0; i < NV; ++i) acc[i] += w * stage[i * S + e];
+    for (int j = 0; j < 4; ++j) {
+      on[j] = l < cnt[j];
+      ent[j] = on[j] ? jds[off] : 0u;   // = jds_entry(D, e, c): word offset of the first plane to read
+      off += cnt[j];
     }
+    float v[4][D];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (MODE == G_STAR) {
+#pragma unroll
+        for (int i = 0; i < D; ++i) v[j][i] = on[j] ? stage[ent[j] + i * S] : 0.f;
+      } else {
+        const int e = ent[j] % S;
+        const float w = ent[j] >= (uint32_t)(D * D * S) ? w0 : 1.f;   // corner 0 entries live past plane D*D
+#pragma unroll
+        for (int i = 0; i < D; ++i) v[j][i] = (on[j] && i < NV) ? w * stage[i * S + e] : 0.f;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int i = 0; i < D; ++i) acc[i] += v[j][i];
   }
 }
 

@@ -25,6 +25,16 @@ namespace femb {
 #endif
 constexpr int kStride = FEMB_TILE_CAP;
 
+// Threads per CTA of the tile kernels and the CTAs per SM the register allocation aims at.
+#ifndef FEMB_BLOCK
+#define FEMB_BLOCK 256
+#endif
+#ifndef FEMB_MIN_CTAS
+#define FEMB_MIN_CTAS 2
+#endif
+constexpr int kBlock = FEMB_BLOCK;
+constexpr int kMinCtas = FEMB_MIN_CTAS;
+
 // JDS entry of (element slot e in tile, corner c): the staging-plane word offset the gather
 // reads first.  Corner j>=1 owns planes (j-1)*dim .. +dim-1 (column j-1 of the element's
 // contribution matrix), corner 0 owns planes dim*dim .. +dim-1 (minus the column sum).

@@ -13,7 +13,7 @@ import subprocess
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libfemb200.so")
+LIB_PATH = os.environ.get("FEMB200_LIB") or os.path.join(_HERE, "libfemb200.so")  # env override: tuning builds
 CSRC = os.path.join(os.path.dirname(_HERE), "csrc")
 
 # femb_field
