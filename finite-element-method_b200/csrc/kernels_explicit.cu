@@ -82,6 +82,7 @@ struct OpSetup {
     uint32_t w0, w1;
   };
   __device__ static void prefetch(const Args&, int, uint32_t) {}
+  __device__ static void prefetch_verts(const Args&, int, uint32_t) {}
   __device__ static void load(const Args& a, int slot, Elem& d) {
     d.w0 = a.lidx[2 * slot];
     d.w1 = a.lidx[2 * slot + 1];
@@ -137,7 +138,8 @@ struct OpSetup {
     // mass[v] += 1/(dim+1) * V * rho          (object.py:358-360)
     out[0] = __fmul_rn(__fmul_rn((float)(1.0 / (D + 1)), vol), a.mat.rho);
   }
-  __device__ static void vertex(const Args& a, int gid, float4, const float (&acc)[D], float&) {
+  __device__ static float4 pre(const Args&, int) { return make_float4(0.f, 0.f, 0.f, 0.f); }
+  __device__ static void vertex(const Args& a, int gid, float4, float4, const float (&acc)[D], float&) {
     a.vs.pos[gid].w = acc[0];
   }
 };
@@ -165,6 +167,12 @@ struct OpExplicit {
 
   using Elem = PlaneElem;
   __device__ static void prefetch(const Args& a, int slot, uint32_t bytes) { prefetch_planes(a.e, slot, bytes, D == 3); }
+  // interior vertices of a tile are one contiguous id range: pos (+ vel / force) of the next tile
+  __device__ static void prefetch_verts(const Args& a, int base, uint32_t bytes) {
+    bulk_prefetch_l2(a.vs.pos + base, bytes);
+    if (MODE == EX_STEP) bulk_prefetch_l2(a.vs.vel + base, bytes);
+    if (MODE == EX_GRAD) bulk_prefetch_l2(a.vs.force + base, bytes);
+  }
   __device__ static void load(const Args& a, int slot, Elem& d) { load_planes<D>(a.e, slot, d); }
   __device__ static void compute(const Args& a, int slot, const Elem& d, const float4* sv, float (&out)[NSTAGE],
                                  float& red) {
@@ -206,15 +214,21 @@ struct OpExplicit {
     }
   }
 
-  __device__ static void vertex(const Args& a, int gid, float4 p, const float (&acc)[D], float&) {
+  // the vertex operand the epilogue updates: force (EX_GRAD) or vel (EX_STEP)
+  __device__ static float4 pre(const Args& a, int gid) {
+    if (MODE == EX_GRAD) return a.vs.force[gid];
+    if (MODE == EX_STEP) return a.vs.vel[gid];
+    return make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  __device__ static void vertex(const Args& a, int gid, float4 p, float4 pre, const float (&acc)[D], float&) {
     if (MODE == EX_GRAD) {
-      float4 f = a.vs.force[gid];                                         // force[v] += f (explicit.py:42-49)
+      float4 f = pre;                                                     // force[v] += f (explicit.py:42-49)
       f.x += acc[0]; f.y += acc[1]; if (D == 3) f.z += acc[D - 1];
       a.vs.force[gid] = f;
     } else if (MODE == EX_ENERGY) {
       a.vs.grad[gid] = make_float4(acc[0], acc[1], D == 3 ? acc[D - 1] : 0.f, 0.f);
     } else {
-      float4 v = a.vs.vel[gid];
+      float4 v = pre;
       kinematic_update<D>(p, v, acc, a.kin);
       a.vs.pos[gid] = p;
       a.vs.vel[gid] = v;

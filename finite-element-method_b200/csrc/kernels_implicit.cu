@@ -34,6 +34,10 @@ struct OpAssemble {
 
   using Elem = PlaneElem;
   __device__ static void prefetch(const Args& a, int slot, uint32_t bytes) { prefetch_planes(a.e, slot, bytes, D == 3); }
+  __device__ static void prefetch_verts(const Args& a, int base, uint32_t bytes) {
+    bulk_prefetch_l2(a.vs.pos + base, bytes);
+    bulk_prefetch_l2(a.vs.vel + base, bytes);
+  }
   __device__ static void load(const Args& a, int slot, Elem& d) { load_planes<D>(a.e, slot, d); }
   __device__ static void compute(const Args& a, int slot, const Elem& d, const float4* sv, float (&out)[NSTAGE],
                                  float&) {
@@ -95,10 +99,11 @@ struct OpAssemble {
     a.h.p1[slot] = h1;
   }
 
-  __device__ static void vertex(const Args& a, int gid, float4 p, const float (&acc)[D], float&) {
+  __device__ static float4 pre(const Args& a, int gid) { return a.vs.vel[gid]; }
+  __device__ static void vertex(const Args& a, int gid, float4 p, float4 vel, const float (&acc)[D], float&) {
     // b = vel ; b[v] += dt * (1/m_v) * f_v              (implicit.py:67-68, 98-105)
     const float s = a.dt * (1.f / p.w);
-    float4 b = a.vs.vel[gid];
+    float4 b = vel;
     b.x += s * acc[0]; b.y += s * acc[1]; if (D == 3) b.z += s * acc[D - 1];
     b.w = 0.f;
     a.iv.b[gid] = b;
@@ -123,6 +128,7 @@ struct OpDiag {
   __device__ static float4 load_vertex(const Args& a, int gid) { return a.vs.pos[gid]; }
   using Elem = PlaneElem;
   __device__ static void prefetch(const Args& a, int slot, uint32_t bytes) { prefetch_planes(a.h, slot, bytes, D == 3); }
+  __device__ static void prefetch_verts(const Args& a, int base, uint32_t bytes) { bulk_prefetch_l2(a.vs.pos + base, bytes); }
   __device__ static void load(const Args& a, int slot, Elem& d) { load_planes<D>(a.h, slot, d); }
   __device__ static void compute(const Args&, int, const Elem& d, const float4*, float (&out)[NSTAGE], float&) {
     const float4 h0 = d.a, h1 = d.b;
@@ -132,7 +138,8 @@ struct OpDiag {
       out[0] = h0.z; out[1] = h1.y;
     }
   }
-  __device__ static void vertex(const Args& a, int gid, float4 p, const float (&acc)[D], float&) {
+  __device__ static float4 pre(const Args&, int) { return make_float4(0.f, 0.f, 0.f, 0.f); }
+  __device__ static void vertex(const Args& a, int gid, float4 p, float4, const float (&acc)[D], float&) {
     const float s = a.dt2 * (1.f / p.w);
     a.iv.diag[gid] = make_float4(1.f - s * acc[0], 1.f - s * acc[1], D == 3 ? 1.f - s * acc[D - 1] : 1.f, 0.f);
   }
@@ -172,6 +179,10 @@ struct OpApply {
   }
   using Elem = PlaneElem;
   __device__ static void prefetch(const Args& a, int slot, uint32_t bytes) { prefetch_planes(a.h, slot, bytes, D == 3); }
+  __device__ static void prefetch_verts(const Args& a, int base, uint32_t bytes) {
+    bulk_prefetch_l2(a.in + base, bytes);
+    bulk_prefetch_l2(a.pos + base, bytes);
+  }
   __device__ static void load(const Args& a, int slot, Elem& d) { load_planes<D>(a.h, slot, d); }
   __device__ static void compute(const Args&, int, const Elem& d, const float4* sv, float (&out)[NSTAGE], float&) {
     const float4 h0 = d.a, h1 = d.b, h2 = d.c;
@@ -188,9 +199,14 @@ struct OpApply {
         out[j * D + i] = s;
       }
   }
-  __device__ static void vertex(const Args& a, int gid, float4, const float (&acc)[D], float& red) {
-    const float4 d = a.in[gid];
-    const float s = TR ? a.dt2 : a.dt2 * (1.f / a.pos[gid].w);
+  // {in.xyz, mass}: the un-scaled input vector and the row scale of the epilogue
+  __device__ static float4 pre(const Args& a, int gid) {
+    float4 d = a.in[gid];
+    d.w = TR ? 1.f : a.pos[gid].w;
+    return d;
+  }
+  __device__ static void vertex(const Args& a, int gid, float4, float4 d, const float (&acc)[D], float& red) {
+    const float s = TR ? a.dt2 : a.dt2 * (1.f / d.w);
     float4 q;
     q.x = d.x - s * acc[0];
     q.y = d.y - s * acc[1];

@@ -150,6 +150,9 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile(DevTiling tl, 
     if (tl.prefetch_dist > 0 && nxt < tl.n_tiles) {
       const TileDesc tn = tl.tiles[nxt];
       Op::prefetch(a, tn.slot_off, (uint32_t)(round_up(tn.n_elem, 32) * 16));
+      bulk_prefetch_l2(tl.lv + tn.lv_off, (uint32_t)round_up(tn.n_lv * 8, 16));
+      bulk_prefetch_l2(tl.jds + tn.jds_off, (uint32_t)round_up(tn.n_elem * tl.nc * 2, 16));
+      if (tn.n_int > 0) Op::prefetch_verts(a, tn.int_base, (uint32_t)(tn.n_int * 16));
     }
   }
   const int B = blockDim.x;
@@ -194,12 +197,15 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile(DevTiling tl, 
   mbar_wait(&s_bar[1], 0);
 
   for (int l = threadIdx.x; l < td.n_lv; l += B) {
+    const LocalVert v = s_lv[l];
+    // per-vertex global operand of the epilogue (e.g. vel): requested before the gather hides its latency
+    float4 pre = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (v.part < 0) pre = Op::pre(a, v.gid);
     float acc[D];
     gather_local_vertex<D, Op::GATHER, (Op::NSTAGE < D ? Op::NSTAGE : D)>(td.n_rounds, s_rounds, s_jds, stage, l,
                                                                          Op::w0(), acc);
-    const LocalVert v = s_lv[l];
     if (v.part < 0) {
-      Op::vertex(a, v.gid, sv[l], acc, red);
+      Op::vertex(a, v.gid, sv[l], pre, acc, red);
     } else {
       float4 p;
       p.x = acc[0]; p.y = acc[1]; p.z = D == 3 ? acc[D - 1] : 0.f; p.w = 0.f;
@@ -233,7 +239,7 @@ __global__ void __launch_bounds__(kBoundaryBlock) k_boundary(DevTiling tl, typen
       if (D == 3) acc[D - 1] += p.z;
     }
     const int gid = tl.n_interior + b;
-    Op::vertex(a, gid, Op::load_vertex(a, gid), acc, red);
+    Op::vertex(a, gid, Op::load_vertex(a, gid), Op::pre(a, gid), acc, red);
   }
   if (Op::REDUCE) {
     const float r = block_sum(red, s_warp);

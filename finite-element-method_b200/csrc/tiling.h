@@ -21,7 +21,7 @@ namespace femb {
 // Capacity of a tile in elements == stride (in floats) of one shared-memory staging plane.
 // Compile-time so that every staging access is base register + immediate offset.
 #ifndef FEMB_TILE_CAP
-#define FEMB_TILE_CAP 1536
+#define FEMB_TILE_CAP 768
 #endif
 constexpr int kStride = FEMB_TILE_CAP;
 
@@ -30,7 +30,7 @@ constexpr int kStride = FEMB_TILE_CAP;
 #define FEMB_BLOCK 256
 #endif
 #ifndef FEMB_MIN_CTAS
-#define FEMB_MIN_CTAS 2
+#define FEMB_MIN_CTAS 4
 #endif
 constexpr int kBlock = FEMB_BLOCK;
 constexpr int kMinCtas = FEMB_MIN_CTAS;
