@@ -86,7 +86,7 @@ def test_tile_gather_equals_scatter(case):
     else:  # shuffled element order, permuted corners, a single tile
         verts, el = o.kuhn_box(3, 3, 3, 0.1)
         el = el[rng.permutation(len(el))]
-        T = 1024
+        T = 512
     verts = verts.astype(np.float32)
     nc = el.shape[1]
     t = _capi.HostTiling(verts, el, T)
@@ -134,8 +134,8 @@ def test_tiling_rejects_bad_meshes():
 def test_large_structured_tiling_stats():
     """C3-like spacing at reduced size: tiles are compact (few boundary vertices)."""
     verts, el = o.kuhn_box(24, 24, 24, 0.01)
-    t = _capi.HostTiling(verts.astype(np.float32), el, 1536)
+    t = _capi.HostTiling(verts.astype(np.float32), el, 768)
     info = t.info
-    assert info["n_tiles"] >= len(el) // 1536 and info["stage_stride"] >= 1536
+    assert info["n_tiles"] >= len(el) // 768 and info["stage_stride"] >= 768
     assert info["max_rounds"] == 24            # interior Kuhn valence
     assert info["n_boundary"] < 0.75 * len(verts)
