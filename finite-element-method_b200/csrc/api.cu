@@ -85,7 +85,9 @@ int femb_object_create(const femb_desc* d, femb_object** out) {
 
     int T = d->tile_elems > 0 ? std::min(d->tile_elems, kStride) : kStride;
     for (;;) {
-      const std::string err = build_tiling(dim, d->n_vert, d->n_elem, pos.data(), d->elems, T, o->til);
+      if (d->n_halo < 0 || (d->n_halo > 0 && !d->halo_verts)) throw ArgError("bad halo vertex list");
+      const std::string err = build_tiling(dim, d->n_vert, d->n_elem, pos.data(), d->elems, T, o->til, d->n_halo,
+                                           d->halo_verts);
       if (!err.empty()) throw ArgError(err);
       if (tile_smem_bytes(o->til) <= kMaxSmem) break;
       if (T <= 64) throw LimitError("tiling does not fit shared memory even with 64-element tiles");
@@ -114,6 +116,12 @@ int femb_object_create(const femb_desc* d, femb_object** out) {
     upload(o->d_lidx, t.lidx);
     upload(o->d_new_of_old, t.new_of_old);
     upload(o->d_slot_of_elem, t.slot_of_elem);
+    if (!t.halo_b.empty()) {
+      int32_t* d_hb;
+      upload(d_hb, t.halo_b);
+      o->halo.n = (int)t.halo_b.size();
+      o->halo.b = d_hb;
+    }
     // CTAs of the tile kernels resident at once = how far ahead the L2 prefetch looks
     const int occ = std::max(1, std::min(2048 / kBlock, (227 * 1024) / (tile_smem_bytes(t) + 1024)));
     o->dtl = DevTiling{d_tiles, d_lv, d_jds, d_rounds, d_bptr, t.n_tiles, t.n_interior, t.n_boundary, t.n_vert,
@@ -227,6 +235,7 @@ int femb_explicit_grad(femb_object* o) {
   FEMB_TRY
   if (!o) throw ArgError("NULL object");
   FEMB_CUDA(cudaSetDevice(o->device));
+  o->prep_full_pass();
   launch_explicit(o->dim, EX_GRAD, o->cfg, o->dtl, o->e, o->vs, o->mat, KinArgs{}, nullptr, nullptr);
   FEMB_CATCH
 }
@@ -235,6 +244,7 @@ int femb_energy_grad(femb_object* o, float* U_out) {
   FEMB_TRY
   if (!o) throw ArgError("NULL object");
   FEMB_CUDA(cudaSetDevice(o->device));
+  o->prep_full_pass();
   launch_explicit(o->dim, EX_ENERGY, o->cfg, o->dtl, o->e, o->vs, o->mat, KinArgs{}, o->d_phi, o->d_red);
   const int nbb = (o->dtl.n_boundary + 255) / 256;
   launch_reduce_final(o->cfg, o->dtl.n_tiles + nbb, o->d_red, o->d_U);
@@ -265,6 +275,7 @@ int femb_explicit_step(femb_object* o, float dt, const float* g_dir, int32_t n_s
   if (!o || n_steps < 0) throw ArgError("femb_explicit_step: bad argument");
   FEMB_CUDA(cudaSetDevice(o->device));
   const KinArgs kin = o->kin_args(dt, g_dir);
+  o->prep_full_pass();
   auto run = [&]() {
     for (int s = 0; s < n_steps; ++s)
       launch_explicit(o->dim, EX_STEP, o->cfg, o->dtl, o->e, o->vs, o->mat, kin, nullptr, nullptr);
@@ -329,6 +340,45 @@ int femb_explicit_step_timed(femb_object* o, float dt, const float* g_dir, int32
   for (auto& e : ev) cudaEventDestroy(e);
   *tile_ms = (float)t;
   *boundary_ms = (float)b;
+  FEMB_CATCH
+}
+
+int femb_halo_bind(femb_object* o, void* send_dev, void* recv_dev) {
+  FEMB_TRY
+  if (!o) throw ArgError("NULL object");
+  if (o->halo.n == 0) throw StateError("object was created without halo vertices");
+  if (!send_dev || !recv_dev) throw ArgError("femb_halo_bind: NULL buffer");
+  o->halo.send = static_cast<float4*>(send_dev);
+  o->halo.recv = static_cast<float4*>(recv_dev);
+  FEMB_CATCH
+}
+
+static void need_halo(const femb_object* o, int phase) {
+  if (!o) throw ArgError("NULL object");
+  if (phase != 1 && phase != 2) throw ArgError("phase must be 1 or 2");
+  if (o->halo.n == 0 || !o->halo.send || !o->halo.recv) throw StateError("halo buffers are not bound");
+}
+
+int femb_halo_mass(femb_object* o, int32_t phase) {
+  FEMB_TRY
+  need_halo(o, phase);
+  FEMB_CUDA(cudaSetDevice(o->device));
+  launch_halo_mass(o->cfg, o->dtl, o->halo, o->vs.pos, phase - 1);
+  FEMB_CATCH
+}
+
+int femb_explicit_step_phase(femb_object* o, float dt, const float* g_dir, int32_t phase) {
+  FEMB_TRY
+  need_halo(o, phase);
+  FEMB_CUDA(cudaSetDevice(o->device));
+  LaunchCfg cfg = o->cfg;
+  cfg.phase = phase;
+  if (phase == 2) {
+    launch_halo_unpack(cfg, o->dtl, o->halo, o->vs.partial);
+    o->halo_dirty = true;
+  }
+  launch_explicit(o->dim, EX_STEP, cfg, o->dtl, o->e, o->vs, o->mat, o->kin_args(dt, g_dir), nullptr, nullptr);
+  if (phase == 1) launch_halo_pack(cfg, o->dtl, o->halo, o->vs.partial);
   FEMB_CATCH
 }
 

@@ -29,6 +29,7 @@ static void poll(femb_object* o) {
 }
 
 static void assemble(femb_object* o, float dt, bool with_diag) {
+  o->prep_full_pass();
   launch_implicit_assemble(o->dim, o->cfg, o->dtl, o->e, o->h, o->vs, o->mat, dt, o->iv);
   if (with_diag) launch_implicit_diag(o->dim, o->cfg, o->dtl, o->h, o->vs, dt, o->iv);
 }

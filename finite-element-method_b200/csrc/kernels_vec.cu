@@ -322,4 +322,59 @@ void launch_pack_elem(const LaunchCfg& c, int dim, int n_elem, const int32_t* sl
   note_launch("pack_elem", c.stream);
 }
 
+// ---------------------------------------------------------------------------
+// halo (multi-GPU slabs): a shared vertex has its local partial slots first and ONE remote slot last.
+// Both ranks compute (sum of local slots) and exchange it, so each evaluates local + remote =
+// remote + local: the same two-term fp32 sum on both sides (bit-identical shared vertices).
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_halo_pack(int n, const int32_t* hb, const int32_t* bptr, const float4* partial,
+                                                   float4* send) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int b = hb[k];
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int i = bptr[b]; i < bptr[b + 1] - 1; ++i) {   // same order as k_boundary
+    const float4 p = partial[i];
+    s.x += p.x; s.y += p.y; s.z += p.z;
+  }
+  send[k] = s;
+}
+
+__global__ void __launch_bounds__(256) k_halo_unpack(int n, const int32_t* hb, const int32_t* bptr, float4* partial,
+                                                     const float4* recv, int zero) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  partial[bptr[hb[k] + 1] - 1] = zero ? make_float4(0.f, 0.f, 0.f, 0.f) : recv[k];
+}
+
+__global__ void __launch_bounds__(256) k_halo_mass(int n, const int32_t* hb, int n_interior, float4* pos, float4* send,
+                                                   const float4* recv, int phase) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int gid = n_interior + hb[k];
+  if (phase == 0) send[k] = make_float4(pos[gid].w, 0.f, 0.f, 0.f);
+  else pos[gid].w += recv[k].x;
+}
+
+void launch_halo_pack(const LaunchCfg& c, const DevTiling& tl, Halo h, const float4* partial) {
+  if (h.n == 0) return;
+  k_halo_pack<<<nblk(h.n), 256, 0, c.stream>>>(h.n, h.b, tl.bptr, partial, h.send);
+  note_launch("halo_pack", c.stream);
+}
+void launch_halo_unpack(const LaunchCfg& c, const DevTiling& tl, Halo h, float4* partial) {
+  if (h.n == 0) return;
+  k_halo_unpack<<<nblk(h.n), 256, 0, c.stream>>>(h.n, h.b, tl.bptr, partial, h.recv, 0);
+  note_launch("halo_unpack", c.stream);
+}
+void launch_halo_zero_remote(const LaunchCfg& c, const DevTiling& tl, Halo h, float4* partial) {
+  if (h.n == 0) return;
+  k_halo_unpack<<<nblk(h.n), 256, 0, c.stream>>>(h.n, h.b, tl.bptr, partial, nullptr, 1);
+  note_launch("halo_zero", c.stream);
+}
+void launch_halo_mass(const LaunchCfg& c, const DevTiling& tl, Halo h, float4* pos, int phase) {
+  if (h.n == 0) return;
+  k_halo_mass<<<nblk(h.n), 256, 0, c.stream>>>(h.n, h.b, tl.n_interior, pos, h.send, h.recv, phase);
+  note_launch("halo_mass", c.stream);
+}
+
 }  // namespace femb

@@ -47,7 +47,22 @@ struct LaunchCfg {
   int sms;
   int device;
   cudaEvent_t ev_mid = nullptr;  // if set, recorded between the tile and the boundary kernel of a pass
+  int phase = 0;                 // 0: tile + boundary kernel; 1: tile kernel only; 2: boundary kernel only
+                                 // (multi-GPU: the halo exchange of the partial sums runs between 1 and 2)
 };
+
+struct Halo {                    // vertices shared with a neighbouring rank (slab interface planes)
+  int n = 0;
+  const int32_t* b = nullptr;    // [n] boundary index of each halo vertex
+  float4* send = nullptr;        // [n] caller-owned device buffers (torch tensors / peer memory)
+  float4* recv = nullptr;
+};
+// send[k] = sum of the local partial slots of halo vertex k ; partial[remote slot of k] = recv[k]
+void launch_halo_pack(const LaunchCfg& c, const DevTiling& tl, Halo h, const float4* partial);
+void launch_halo_unpack(const LaunchCfg& c, const DevTiling& tl, Halo h, float4* partial);
+// lumped mass of shared vertices: phase 0 send[k].x = local mass ; phase 1 mass += recv[k].x
+void launch_halo_mass(const LaunchCfg& c, const DevTiling& tl, Halo h, float4* pos, int phase);
+void launch_halo_zero_remote(const LaunchCfg& c, const DevTiling& tl, Halo h, float4* partial);
 
 // setup: Dm^-1, volume -> element planes; lumped mass -> pos.w   (object.py:345-362)
 void launch_setup(int dim, const LaunchCfg& c, const DevTiling& tl, Planes e, const uint32_t* lidx,

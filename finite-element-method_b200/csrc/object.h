@@ -66,6 +66,15 @@ struct femb_object {
   bool own_stream = false;
   femb::LaunchCfg cfg{};
   femb::StepGraph graph;
+  femb::Halo halo;                  // multi-GPU: vertices shared with neighbouring ranks
+  bool halo_dirty = false;          // remote partial slots hold data of an earlier exchange
+  // every un-phased pass on a halo object must see zeros in the remote slots
+  void prep_full_pass() {
+    if (halo.n && halo_dirty) {
+      femb::launch_halo_zero_remote(cfg, dtl, halo, vs.partial);
+      halo_dirty = false;
+    }
+  }
   std::vector<void*> allocs;
   int64_t device_bytes = 0;
 

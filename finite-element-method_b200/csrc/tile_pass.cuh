@@ -266,10 +266,12 @@ inline void run_tile_pass(const char* name, const LaunchCfg& c, const DevTiling&
     }
     attr_set[c.device & 63] = smem;
   }
-  k_tile<D, Op><<<tl.n_tiles, Op::BLOCK, smem, c.stream>>>(tl, a);
-  note_launch(name, c.stream);
+  if (c.phase != 2) {
+    k_tile<D, Op><<<tl.n_tiles, Op::BLOCK, smem, c.stream>>>(tl, a);
+    note_launch(name, c.stream);
+  }
   if (c.ev_mid) cudaEventRecord(c.ev_mid, c.stream);
-  if (tl.n_boundary > 0) {
+  if (tl.n_boundary > 0 && c.phase != 1) {
     const int nb = (tl.n_boundary + kBoundaryBlock - 1) / kBoundaryBlock;
     k_boundary<D, Op><<<nb, kBoundaryBlock, 0, c.stream>>>(tl, a, tl.n_tiles);
     note_launch(name, c.stream);

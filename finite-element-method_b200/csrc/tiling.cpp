@@ -70,7 +70,7 @@ struct Rcb {
 }  // namespace
 
 std::string build_tiling(int dim, int n_vert, int n_elem, const float* verts,
-                         const int32_t* elems, int tile_elems, Tiling& t) {
+                         const int32_t* elems, int tile_elems, Tiling& t, int n_halo, const int32_t* halo_verts) {
   if (dim != 2 && dim != 3) return "dim must be 2 or 3";
   if (n_vert <= 0 || n_elem <= 0) return "empty mesh";
   if (!verts || !elems) return "null mesh arrays";
@@ -133,6 +133,12 @@ std::string build_tiling(int dim, int n_vert, int n_elem, const float* verts,
   }
   for (int v = 0; v < n_vert; ++v)
     if (tcount[v].load(std::memory_order_relaxed) == 0) return "mesh has a vertex that no element references";
+  // halo vertices (shared with another rank) are never finished inside a tile: force them into the
+  // boundary class; they also get one extra, LAST partial slot that receives the remote rank's sum
+  for (int k = 0; k < n_halo; ++k) {
+    if (halo_verts[k] < 0 || halo_verts[k] >= n_vert) return "halo vertex index out of range";
+    tcount[halo_verts[k]].fetch_add(1 << 20, std::memory_order_relaxed);
+  }
 
   // 4. per tile: in-tile valence, local order (valence descending, then old id)
   std::vector<std::vector<int32_t>> tval(nt);   // valence in local order
@@ -215,6 +221,13 @@ std::string build_tiling(int dim, int n_vert, int n_elem, const float* verts,
     if (nb != t.n_boundary) return "internal error: boundary count mismatch";
   }
   for (int v = 0; v < n_vert; ++v) t.old_of_new[t.new_of_old[v]] = v;
+  t.halo_b.resize(n_halo);
+  for (int k = 0; k < n_halo; ++k) {
+    const int b = t.new_of_old[halo_verts[k]] - t.n_interior;
+    if ((tcount[halo_verts[k]].load(std::memory_order_relaxed) >> 20) != 1) return "duplicate halo vertex";
+    t.halo_b[k] = b;
+    bcount[b]++;   // the remote slot
+  }
   t.bptr.assign(t.n_boundary + 1, 0);
   for (int b = 0; b < t.n_boundary; ++b) t.bptr[b + 1] = t.bptr[b] + bcount[b];
   t.n_partials = t.bptr[t.n_boundary];

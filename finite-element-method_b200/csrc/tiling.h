@@ -73,11 +73,13 @@ struct Tiling {
   std::vector<uint32_t> rounds;   // per tile, per round k: #local vertices with valence > k
   std::vector<uint32_t> lidx;     // per slot: 2 x uint32 = 4 x uint16 local corner indices
   std::vector<int32_t> bptr;      // [n_boundary+1] partial-slot range of each boundary vertex
+  std::vector<int32_t> halo_b;    // boundary index of each halo vertex; its remote slot is bptr[b+1]-1
 };
 
 // verts: [n_vert*dim] positions used only for spatial grouping.  Returns an
 // empty string on success, else an error message.
 std::string build_tiling(int dim, int n_vert, int n_elem, const float* verts,
-                         const int32_t* elems, int tile_elems, Tiling& out);
+                         const int32_t* elems, int tile_elems, Tiling& out, int n_halo = 0,
+                         const int32_t* halo_verts = nullptr);
 
 }  // namespace femb

@@ -23,6 +23,7 @@ F_ELEM_VOLUME, F_ELEM_REF, F_ELEM_PHI, F_ELEM_H = 32, 33, 34, 35
 EXPORTS = [
     "femb_object_create", "femb_object_destroy", "femb_object_info", "femb_set_stream", "femb_blocks_set",
     "femb_explicit_grad", "femb_energy_grad", "femb_kinematic", "femb_explicit_step", "femb_explicit_step_timed", "femb_implicit_solve",
+    "femb_halo_bind", "femb_halo_mass", "femb_explicit_step_phase",
     "femb_advect_implicit", "femb_implicit_assemble", "femb_implicit_apply", "femb_get", "femb_set",
     "femb_get_energy", "femb_sync", "femb_last_error", "femb_launch_count", "femb_version",
     "femb_tiling_build", "femb_tiling_destroy", "femb_tiling_info", "femb_tiling_get",
@@ -36,6 +37,7 @@ class Desc(C.Structure):
         ("center", C.c_float * 3),
         ("rho", C.c_float), ("mu", C.c_float), ("lam", C.c_float), ("damping", C.c_float),
         ("implicit", C.c_int32), ("tile_elems", C.c_int32), ("device", C.c_int32),
+        ("n_halo", C.c_int32), ("halo_verts", C.POINTER(C.c_int32)),
     ]
 
 
@@ -79,6 +81,9 @@ def lib():
         "femb_kinematic": (C.c_int, [vp, f32, fp, i32]),
         "femb_explicit_step": (C.c_int, [vp, f32, fp, i32]),
         "femb_explicit_step_timed": (C.c_int, [vp, f32, fp, i32, fp, fp]),
+        "femb_halo_bind": (C.c_int, [vp, vp, vp]),
+        "femb_halo_mass": (C.c_int, [vp, i32]),
+        "femb_explicit_step_phase": (C.c_int, [vp, f32, fp, i32]),
         "femb_implicit_solve": (C.c_int, [vp, f32, i32, i32, i32, f32, ip, fp]),
         "femb_advect_implicit": (C.c_int, [vp, f32, fp]),
         "femb_implicit_assemble": (C.c_int, [vp, f32]),
@@ -127,8 +132,8 @@ class Handle:
 
     def __init__(self, verts, elems, center, rho, mu, lam, damping, implicit=False, tile_elems=0, device=-1,
                  halo_verts=None):
-        if halo_verts is not None:
-            raise NotImplementedError("halo vertices: multi-GPU slabs are not wired up yet")
+        halo = np.ascontiguousarray(halo_verts if halo_verts is not None else [], dtype=np.int32)
+        self.n_halo = int(halo.size)
         verts = np.ascontiguousarray(verts, dtype=np.float32)
         elems = np.ascontiguousarray(elems, dtype=np.int32)
         self.dim = int(verts.shape[1])
@@ -143,6 +148,7 @@ class Handle:
         d.center = (C.c_float * 3)(*c.tolist())
         d.rho, d.mu, d.lam, d.damping = float(rho), float(mu), float(lam), float(damping)
         d.implicit, d.tile_elems, d.device = int(bool(implicit)), int(tile_elems), int(device)
+        d.n_halo, d.halo_verts = self.n_halo, _iptr(halo)
         self._h = C.c_void_p()
         check(lib().femb_object_create(C.byref(d), C.byref(self._h)))
 
@@ -215,6 +221,17 @@ class Handle:
     def explicit_step(self, dt, g_dir, n_steps=1):
         g = gvec(g_dir, self.dim)
         check(lib().femb_explicit_step(self._h, float(dt), _fptr(g), int(n_steps)))
+
+    # -- multi-GPU halo
+    def halo_bind(self, send_ptr, recv_ptr):
+        check(lib().femb_halo_bind(self._h, C.c_void_p(int(send_ptr)), C.c_void_p(int(recv_ptr))))
+
+    def halo_mass(self, phase):
+        check(lib().femb_halo_mass(self._h, int(phase)))
+
+    def explicit_step_phase(self, dt, g_dir, phase):
+        g = gvec(g_dir, self.dim)
+        check(lib().femb_explicit_step_phase(self._h, float(dt), _fptr(g), int(phase)))
 
     def explicit_step_timed(self, dt, g_dir, n_steps):
         g = gvec(g_dir, self.dim)

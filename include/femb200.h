@@ -70,6 +70,12 @@ typedef struct femb_desc {
   int32_t implicit;     /* !=0: allocate the implicit-solver vectors, object.py:78-93 */
   int32_t tile_elems;   /* elements per tile (<= femb_info.stage_stride); 0 = library default */
   int32_t device;       /* CUDA device ordinal; -1 = current device */
+  /* Multi-GPU (one process per GPU, mesh partitioned by the caller): vertices of THIS rank's
+   * mesh that another rank also holds.  Each may appear once; the element gradient / operator
+   * output on them is completed by a halo exchange (femb_halo_* below).  Not in the reference
+   * (single device, main.py:40). */
+  int32_t n_halo;
+  const int32_t *halo_verts; /* [n_halo] original vertex ids */
 } femb_desc;
 
 typedef struct femb_info {
@@ -109,6 +115,17 @@ int femb_explicit_step(femb_object *obj, float dt, const float *g_dir, int32_t n
  * Measurement aid for bench.py's per-kernel roofline; synchronises. */
 int femb_explicit_step_timed(femb_object *obj, float dt, const float *g_dir, int32_t n_steps,
                              float *tile_ms, float *boundary_ms);
+
+/* ---- multi-GPU halo (new: the reference is single-device).  send/recv are caller-owned DEVICE
+ * buffers of n_halo float4 each (torch tensors, NCCL or peer-mapped memory), in halo_verts order.
+ * A phased pass is: phase 1 (tile kernel + pack into send) ; caller exchanges send -> the
+ * neighbour's recv ; phase 2 (unpack recv + boundary kernel).  Shared vertices come out
+ * bit-identical on both ranks (two-term commutative sum). */
+int femb_halo_bind(femb_object *obj, void *send_dev, void *recv_dev);
+/* lumped mass of shared vertices, once after creation: phase 1 packs, phase 2 adds the remote part */
+int femb_halo_mass(femb_object *obj, int32_t phase);
+/* one fused explicit step split around the exchange (phase 1 | exchange | phase 2) */
+int femb_explicit_step_phase(femb_object *obj, float dt, const float *g_dir, int32_t phase);
 
 /* ---- implicit path */
 /* implicit_solver_neo_hookean(obj), implicit.py:201-223, matrix-free.

@@ -1,0 +1,84 @@
+"""Multi-GPU slab path.  CPU part (gloo, world_size 2): partition helpers and the P2P exchange
+pattern of SlabHalo.  GPU part: 2-rank slab run vs the single-GPU run (needs >= 2 GPUs)."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_slab_partition_helpers():
+    from femb200 import dist as fdist, meshgen
+
+    nx, ny, nz = 7, 3, 2
+    plane = (ny + 1) * (nz + 1)
+    covered = []
+    for world in (1, 2, 3, 4):
+        owned = 0
+        for r in range(world):
+            i0, i1 = fdist.slab_range(nx, r, world)
+            covered.append((i0, i1))
+            ids, nl, nr = fdist.slab_halo_vertices(r, world, i1 - i0, ny, nz)
+            assert nl == (plane if r > 0 else 0) and nr == (plane if r < world - 1 else 0)
+            verts, tets = meshgen.kuhn_box(nx, ny, nz, 0.1, x_cells=(i0, i1))
+            assert len(verts) == (i1 - i0 + 1) * plane and len(tets) == (i1 - i0) * ny * nz * 6
+            gverts, _ = meshgen.kuhn_box(nx, ny, nz, 0.1)
+            assert np.allclose(verts, gverts[i0 * plane:(i1 + 1) * plane])
+            if nr:   # my right plane is the neighbour's left plane, same (j,k) order
+                assert np.array_equal(ids[nl:] - (i1 - i0) * plane, np.arange(plane))
+            owned += int(fdist.owner_mask(r, world, i1 - i0, ny, nz).sum())
+        assert owned == (nx + 1) * plane     # every global vertex counted exactly once
+        assert fdist.slab_range(nx, world - 1, world)[1] == nx
+
+
+def _gloo_worker(rank, world, port, q):
+    import torch
+    import torch.distributed as dist
+
+    sys.path[:0] = [os.path.join(ROOT, "finite-element-method_b200"), ROOT]
+    from femb200 import dist as fdist
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    halo = fdist.SlabHalo(rank, world, 3, 2, 2)
+    halo.send = torch.full((halo.n, 4), float(rank + 1))
+    halo.recv = torch.zeros((halo.n, 4))
+    halo.exchange()
+    nl = halo.n_left
+    ok = True
+    if nl:
+        ok &= bool((halo.recv[:nl] == float(rank)).all())        # from rank-1
+    if halo.n_right:
+        ok &= bool((halo.recv[nl:] == float(rank + 2)).all())     # from rank+1
+    q.put((rank, ok))
+    dist.destroy_process_group()
+
+
+def test_halo_exchange_pattern_gloo_world2():
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + os.getpid() % 2000
+    procs = [ctx.Process(target=_gloo_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+    assert res == [(0, True), (1, True)]
+
+
+@pytest.mark.gpu
+def test_two_rank_slabs_match_single_gpu():
+    import torch
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29611",
+                        os.path.join(ROOT, "tests", "mp_slab_check.py")], capture_output=True, text=True, timeout=600)
+    assert "SLAB_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
