@@ -159,7 +159,8 @@ def run_ours(args):
         from femb200 import dist as fdist
         halo = fdist.SlabHalo(rank, world, i1 - i0, ny, nz)
     h = c.Handle(verts, tets, center, MAT["rho"], mu, lam, MAT["damping"], implicit=(kind != "explicit"),
-                 tile_elems=args.tile, device=local_rank, halo_verts=None if halo is None else halo.vertex_ids)
+                 tile_elems=args.tile, device=local_rank, halo_verts=None if halo is None else halo.vertex_ids,
+                 halo_owned=None if halo is None else halo.owned)
     stream = torch.cuda.Stream()          # a real stream: the legacy default stream cannot be graph-captured
     torch.cuda.set_stream(stream)
     h.set_stream(stream.cuda_stream)
@@ -194,16 +195,18 @@ def run_ours(args):
                     reset_state()
         else:
             # one solve of exactly n iterations (tol = 0 => fixed count, no host polling)
-            h.implicit_solve(dt, 0 if kind == "jacobi" else 1, 1 if kind == "cg_ata" else 0, max_iter=n, tol=0.0,
-                             fetch=False)
+            method, pre = (0 if kind == "jacobi" else 1), (1 if kind == "cg_ata" else 0)
+            if halo is None:
+                h.implicit_solve(dt, method, pre, max_iter=n, tol=0.0, fetch=False)
+            else:
+                halo.implicit_solve(h, dt, method, pre, max_iter=n, tol=0.0, fetch=False)
 
     launches0 = None
     run_steps(args.warmup)
-    if kind == "explicit":
-        # prime the CUDA graph of the timed chunk size (capture + instantiate must not be timed), then
-        # put the state back so the timed region starts from the same configuration
-        run_steps(min(RESET_EVERY, args.steps))
-        reset_state()
+    # prime the CUDA graph of the timed chunk size (capture + instantiate must not be timed), then
+    # put the state back so the timed region starts from the same configuration
+    run_steps(min(RESET_EVERY, args.steps) if kind == "explicit" else args.steps)
+    reset_state()
     barrier()
     replayed0 = getattr(halo, "replayed_launches", 0) if halo is not None else 0
     sampler = ClockSampler(local_rank)
@@ -224,6 +227,13 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     finite = bool(np.isfinite(h.get(c.F_POS)).all())
+    iters_done = None
+    if kind != "explicit":
+        # the solve must really have run `steps` iterations (no early exit on convergence / NaN)
+        finite = finite and bool(np.isfinite(h.get(c.F_VEC_X)).all())
+        iters_done = int(h.last_solve_iters())
+        if iters_done != args.steps:
+            raise SystemExit("solver ran %d iterations, expected %d: timing invalid" % (iters_done, args.steps))
 
     # ---- per-kernel roofline of the dominant kernel (tile kernel), timed live with CUDA events
     roof = None
@@ -267,13 +277,16 @@ def run_ours(args):
                        "dt": dt, "partition": "x-slabs, %d rank(s)" % world, "tile_elems": info["tile_elems"],
                        "n_tiles_rank0": info["n_tiles"], "cache": "inputs %.0f MB per rank > 126 MB L2" %
                        (algorithmic_bytes(kind, len(tets), len(verts)) / 1e6),
-                       "state_reset_every": RESET_EVERY if kind == "explicit" else None, "state_finite": finite},
+                       "state_reset_every": RESET_EVERY if kind == "explicit" else None, "state_finite": finite,
+                       "solver_iterations_run": iters_done},
             "clocks": clocks, "gpu_launches": int(launches), "roofline": roof, "e2e": e2e, "cpu_baseline": cpu,
         }
         print(json.dumps(out))
+    if halo is not None:
+        halo.close()
     h.close()
     if world > 1:
-        dist.destroy_process_group()
+        fdist.shutdown()
 
 
 def measure_e2e(args, h, c, kind, w, pos0, vel0, ne_global, world, torch, barrier, halo=None):

@@ -122,11 +122,17 @@ int femb_object_create(const femb_desc* d, femb_object** out) {
       o->halo.n = (int)t.halo_b.size();
       o->halo.b = d_hb;
     }
+    uint8_t* d_bskip = nullptr;
+    if (d->halo_owned && d->n_halo > 0) {
+      std::vector<uint8_t> bskip((size_t)t.n_boundary, 0);
+      for (int k = 0; k < d->n_halo; ++k) bskip[t.halo_b[k]] = d->halo_owned[k] ? 0 : 1;
+      upload(d_bskip, bskip);
+    }
     // CTAs of the tile kernels resident at once = how far ahead the L2 prefetch looks
     const int occ = std::max(1, std::min(2048 / kBlock, (227 * 1024) / (tile_smem_bytes(t) + 1024)));
     o->dtl = DevTiling{d_tiles, d_lv, d_jds, d_rounds, d_bptr, t.n_tiles, t.n_interior, t.n_boundary, t.n_vert,
                        t.n_slots, (t.max_tile_elems + 31) / 32 * 32, t.max_lv, (t.max_rounds + 3) / 4 * 4, t.nc,
-                       prop.multiProcessorCount * occ};
+                       prop.multiProcessorCount * occ, d_bskip};
 
     const size_t ns = (size_t)t.n_slots, nv = (size_t)t.n_vert;
     o->e.p0 = o->alloc<float4>(ns);

@@ -2,6 +2,11 @@
 // host: assemble once per time step, then matrix-free CG / A^T A-CG / Jacobi
 // iterations whose convergence state lives on the device.  The host only polls
 // the `done` flag every few iterations.
+//
+// The solve is a SolveProgram (object.h): device-work segments separated by
+// communication points.  femb_implicit_solve runs it straight through on one GPU;
+// femb_implicit_solve_begin / _advance / _finish hand the communication points to a
+// caller that owns the collectives (one process per GPU, torch.distributed / NCCL).
 #include <algorithm>
 #include <cstring>
 
@@ -34,6 +39,153 @@ static void assemble(femb_object* o, float dt, bool with_diag) {
   if (with_diag) launch_implicit_diag(o->dim, o->cfg, o->dtl, o->h, o->vs, dt, o->iv);
 }
 
+// ---------------------------------------------------------------------------
+// program construction
+// ---------------------------------------------------------------------------
+namespace {
+
+using PassFn = std::function<void(const LaunchCfg&)>;
+using SumFn = std::function<void(int, const double*)>;
+
+struct Builder {
+  femb_object* o;
+  bool dist;
+  std::vector<SolveOp>* L;
+
+  void add(std::function<void()> f, int comm = FEMB_COMM_NONE) { L->push_back(SolveOp{std::move(f), comm}); }
+
+  // one tile pass (tile kernel + boundary kernel); multi-GPU: split around the halo exchange
+  void pass(PassFn f) {
+    femb_object* ob = o;
+    if (!dist) {
+      add([ob, f] { ob->prep_full_pass(); f(ob->cfg); });
+      return;
+    }
+    add([ob, f] {
+      LaunchCfg c = ob->cfg;
+      c.phase = 1;
+      f(c);
+      launch_halo_pack(c, ob->dtl, ob->halo, ob->vs.partial);
+    }, FEMB_COMM_HALO);
+    add([ob, f] {
+      LaunchCfg c = ob->cfg;
+      c.phase = 2;
+      launch_halo_unpack(c, ob->dtl, ob->halo, ob->vs.partial);
+      ob->halo_dirty = true;
+      f(c);
+    });
+  }
+
+  // global sum of the per-CTA partials red[0..n_red) consumed by a scalar kernel; multi-GPU: the
+  // local sum goes to the bound allreduce buffer, the caller sum-allreduces it, the consumer reads it
+  void gsum(int n_red, SumFn consume) {
+    femb_object* ob = o;
+    if (!dist) {
+      add([ob, n_red, consume] { consume(n_red, ob->d_red); });
+      return;
+    }
+    add([ob, n_red] { launch_reduce_final(ob->cfg, n_red, ob->d_red, ob->d_allred); }, FEMB_COMM_ALLREDUCE);
+    add([ob, consume] { consume(1, ob->d_allred); });
+  }
+};
+
+void build_program(femb_object* o, SolveProgram& P, float dt, int method, int preconditioned, int max_iter, float tol) {
+  const bool dist = o->halo.n > 0;
+  if (dist && (!o->halo.send || !o->halo.recv || !o->d_allred))
+    throw StateError("multi-GPU solve: bind the halo buffers (femb_halo_bind) and the allreduce buffer (femb_reduce_bind) first");
+  P.fixed = (tol == 0.f);                              // benchmark mode: exactly max_iter iterations
+  if (tol < 0.f) tol = 1e-5f;                          // implicit.py:236,341
+  if (max_iter <= 0) max_iter = method == 1 ? 500 : 20000;  // implicit.py:337,237
+  P.method = method;
+  o->last_method = method;
+  P.max_iter = max_iter;
+  const float ktol = P.fixed ? -1.f : tol;
+  const int fixed = P.fixed ? 1 : 0;
+  const int dim = o->dim, nv = o->n_vert, ared = apply_red_slots(o), vred = (nv + 255) / 256;
+  const RedMask mask{o->dtl.n_interior, o->dtl.bskip};
+  ImplicitVecs iv = o->iv;
+  SolveScalars* sc = o->d_sc;
+
+  auto apply = [o, dim, dt](int tr, const float4* in, float4* out, int epi, const float4* aux, float4* resid,
+                            const SolveScalars* s) -> PassFn {
+    return [=](const LaunchCfg& c) {
+      launch_apply(dim, c, o->dtl, o->h, o->vs, dt, tr, in, out, epi, aux, resid, o->d_red, s);
+    };
+  };
+
+  Builder pro{o, dist, &P.prologue}, it{o, dist, &P.iteration};
+  pro.add([o, sc] { launch_scalars_reset(o->cfg, sc); });
+  pro.pass([o, dim, dt](const LaunchCfg& c) {
+    launch_implicit_assemble(dim, c, o->dtl, o->e, o->h, o->vs, o->mat, dt, o->iv);
+  });
+
+  if (method == 1) {
+    // ---- conjugate gradient, implicit.py:311-386
+    const float4* rhs = iv.b;
+    if (preconditioned == 1) {                         // ATb = A^T b, ATA = A^T A (289-299)
+      pro.pass(apply(1, iv.b, iv.atb, AP_PLAIN, nullptr, nullptr, nullptr));
+      pro.pass(apply(0, iv.b, iv.tmp, AP_PLAIN, nullptr, nullptr, nullptr));
+      pro.pass(apply(1, iv.tmp, iv.q, AP_PLAIN, nullptr, nullptr, nullptr));
+      rhs = iv.atb;
+    } else {
+      pro.pass(apply(0, iv.b, iv.q, AP_PLAIN, nullptr, nullptr, nullptr));
+    }
+    pro.add([=] { launch_cg_init(o->cfg, nv, iv, rhs, iv.q, o->d_red, mask); });   // x = b, r = rhs - op(x), d = r
+    pro.gsum(vred, [=](int n, const double* red) { launch_cg_delta0(o->cfg, n, red, sc, ktol, max_iter); });
+
+    if (preconditioned == 1) {
+      it.pass(apply(0, iv.d, iv.tmp, AP_PLAIN, nullptr, nullptr, sc));
+      it.pass(apply(1, iv.tmp, iv.q, AP_DOT, iv.d, nullptr, sc));
+    } else {
+      it.pass(apply(0, iv.d, iv.q, AP_DOT, iv.d, nullptr, sc));
+    }
+    it.gsum(ared, [=](int n, const double* red) { launch_cg_alpha(o->cfg, n, red, sc); });
+    it.add([=] { launch_cg_update_xr(o->cfg, nv, iv, o->d_red, sc, mask); });
+    it.gsum(vred, [=](int n, const double* red) { launch_cg_beta(o->cfg, n, red, sc, ktol, max_iter); });
+    it.add([=] { launch_cg_update_d(o->cfg, nv, iv, sc); });
+  } else {
+    // ---- the reference's damped "Jacobi" (227-262, 391-404) as a true parallel Jacobi
+    pro.pass([o, dim, dt](const LaunchCfg& c) { launch_implicit_diag(dim, c, o->dtl, o->h, o->vs, dt, o->iv); });
+    pro.add([=] { launch_scale_xyz(o->cfg, nv, iv.b, iv.x, 0.5f); });               // x0 = 0.5 b (231-232)
+    it.pass(apply(0, iv.x, iv.tmp, AP_RESID, iv.b, iv.r, sc));
+    it.gsum(ared, [=](int n, const double* red) { launch_jacobi_decide(o->cfg, n, red, sc, tol, max_iter, fixed); });
+    it.add([=] { launch_jacobi_update(o->cfg, nv, iv, sc); });
+  }
+}
+
+// Runs segments up to the next communication point; returns that femb_comm.
+int advance(femb_object* o) {
+  SolveProgram& P = *o->prog;
+  std::vector<SolveOp>& L = P.in_prologue ? P.prologue : P.iteration;
+  while (P.pc < L.size()) {
+    const SolveOp& op = L[P.pc++];
+    op.run();
+    if (op.comm != FEMB_COMM_NONE) return op.comm;
+  }
+  P.pc = 0;
+  if (!P.in_prologue) P.iters_issued++;
+  P.in_prologue = false;
+  return FEMB_COMM_ITER;
+}
+
+void check_solve_args(femb_object* o, int method) {
+  if (!o) throw ArgError("NULL object");
+  if (!o->implicit) throw StateError("object was created without implicit buffers");
+  if (method != 0 && method != 1) throw ArgError("implicit method must be 0 (Jacobi) or 1 (CG)");
+}
+
+void finish(femb_object* o, int32_t* iters_out, float* resid_out) {
+  launch_copy_xyz(o->cfg, o->n_vert, o->iv.x, o->vs.vel);          // vel = x (222-223)
+  if (iters_out || resid_out) {
+    poll(o);
+    if (iters_out) *iters_out = o->h_sc->iters;
+    if (resid_out) *resid_out = o->prog->method == 1 ? (float)o->h_sc->delta_new : (float)o->h_sc->err;
+  }
+  o->prog.reset();
+}
+
+}  // namespace
+
 extern "C" {
 
 int femb_implicit_assemble(femb_object* o, float dt) {
@@ -52,6 +204,7 @@ int femb_implicit_apply(femb_object* o, float dt, int32_t transpose, const float
   FEMB_CUDA(cudaSetDevice(o->device));
   const size_t n = (size_t)o->n_vert * o->dim;
   o->ensure_stage(n);
+  o->prep_full_pass();
   FEMB_CUDA(cudaMemsetAsync(o->iv.d, 0, (size_t)o->n_vert * sizeof(float4), o->stream));
   FEMB_CUDA(cudaMemcpyAsync(o->d_stage, in, n * sizeof(float), cudaMemcpyHostToDevice, o->stream));
   launch_unpack_vertex(o->cfg, o->dim, o->n_vert, o->d_new_of_old, o->d_stage, 0, o->dim, o->iv.d);
@@ -66,74 +219,82 @@ int femb_implicit_apply(femb_object* o, float dt, int32_t transpose, const float
 int femb_implicit_solve(femb_object* o, float dt, int32_t method, int32_t preconditioned, int32_t max_iter,
                         float tol, int32_t* iters_out, float* resid_out) {
   FEMB_TRY
-  if (!o) throw ArgError("NULL object");
-  if (!o->implicit) throw StateError("object was created without implicit buffers");
-  if (method != 0 && method != 1) throw ArgError("implicit method must be 0 (Jacobi) or 1 (CG)");
+  check_solve_args(o, method);
+  if (o->halo.n > 0)
+    throw StateError("object has halo vertices: drive the solve with femb_implicit_solve_begin/_advance/_finish");
   FEMB_CUDA(cudaSetDevice(o->device));
-  const bool fixed_count = (tol == 0.f);            // benchmark mode: exactly max_iter iterations, no polling
-  if (tol < 0.f) tol = 1e-5f;                        // implicit.py:236,341
-  if (max_iter <= 0) max_iter = method == 1 ? 500 : 20000;  // implicit.py:337,237
-  const LaunchCfg& c = o->cfg;
-  const DevTiling& tl = o->dtl;
-  ImplicitVecs& iv = o->iv;
-  const int nv = o->n_vert, ared = apply_red_slots(o), vred = (nv + 255) / 256;
-
-  launch_scalars_reset(c, o->d_sc);
-  assemble(o, dt, method == 0);
+  o->prog.reset(new SolveProgram());
+  SolveProgram& P = *o->prog;
+  build_program(o, P, dt, method, preconditioned, max_iter, tol);
+  advance(o);                                          // prologue (no communication on one GPU)
+  // Jacobi needs one more residual evaluation than updates, plus the pass that sets `done`
+  const int n_it = method == 1 ? P.max_iter : P.max_iter + 2;
   int chunk = 4, since_poll = 0;
   bool finished = false;
+  for (int it = 0; it < n_it && !finished; ++it) {
+    advance(o);
+    if (!P.fixed && ++since_poll >= chunk) {
+      poll(o);
+      finished = (o->h_sc->done | o->h_sc->terminal) != 0;
+      since_poll = 0;
+      chunk = std::min(chunk * 2, 32);
+    }
+  }
+  finish(o, iters_out, resid_out);
+  FEMB_CATCH
+}
 
-  if (method == 1) {
-    // ---- conjugate gradient, implicit.py:311-386
-    const float4* rhs = iv.b;
-    if (preconditioned == 1) {                       // ATb = A^T b, ATA = A^T A (289-299)
-      launch_apply(o->dim, c, tl, o->h, o->vs, dt, 1, iv.b, iv.atb, AP_PLAIN, nullptr, nullptr, o->d_red, nullptr);
-      launch_apply(o->dim, c, tl, o->h, o->vs, dt, 0, iv.b, iv.tmp, AP_PLAIN, nullptr, nullptr, o->d_red, nullptr);
-      launch_apply(o->dim, c, tl, o->h, o->vs, dt, 1, iv.tmp, iv.q, AP_PLAIN, nullptr, nullptr, o->d_red, nullptr);
-      rhs = iv.atb;
-    } else {
-      launch_apply(o->dim, c, tl, o->h, o->vs, dt, 0, iv.b, iv.q, AP_PLAIN, nullptr, nullptr, o->d_red, nullptr);
-    }
-    launch_cg_init(c, nv, iv, rhs, iv.q, o->d_red, o->d_sc, tol, max_iter);   // x = b, r = rhs - op(x), d = r
-    for (int it = 0; it < max_iter && !finished; ++it) {
-      if (preconditioned == 1) {
-        launch_apply(o->dim, c, tl, o->h, o->vs, dt, 0, iv.d, iv.tmp, AP_PLAIN, nullptr, nullptr, o->d_red, o->d_sc);
-        launch_apply(o->dim, c, tl, o->h, o->vs, dt, 1, iv.tmp, iv.q, AP_DOT, iv.d, nullptr, o->d_red, o->d_sc);
-      } else {
-        launch_apply(o->dim, c, tl, o->h, o->vs, dt, 0, iv.d, iv.q, AP_DOT, iv.d, nullptr, o->d_red, o->d_sc);
-      }
-      launch_cg_alpha(c, ared, o->d_red, o->d_sc);
-      launch_cg_update_xr(c, nv, iv, o->d_red, o->d_sc);
-      launch_cg_beta(c, vred, o->d_red, o->d_sc, tol, max_iter);
-      launch_cg_update_d(c, nv, iv, o->d_sc);
-      if (!fixed_count && ++since_poll >= chunk) {
-        poll(o);
-        finished = o->h_sc->done != 0;
-        since_poll = 0;
-        chunk = std::min(chunk * 2, 32);
-      }
-    }
-  } else {
-    // ---- the reference's damped "Jacobi" (227-262, 391-404) as a true parallel Jacobi
-    launch_scale_xyz(c, nv, iv.b, iv.x, 0.5f);      // x0 = 0.5 b (231-232)
-    for (int it = 0; it < max_iter + 2 && !finished; ++it) {
-      launch_apply(o->dim, c, tl, o->h, o->vs, dt, 0, iv.x, iv.tmp, AP_RESID, iv.b, iv.r, o->d_red, o->d_sc);
-      launch_jacobi_decide(c, ared, o->d_red, o->d_sc, tol, max_iter);
-      launch_jacobi_update(c, nv, iv, o->d_sc);
-      if (!fixed_count && ++since_poll >= chunk) {
-        poll(o);
-        finished = (o->h_sc->done | o->h_sc->terminal) != 0;
-        since_poll = 0;
-        chunk = std::min(chunk * 2, 32);
-      }
-    }
+int femb_reduce_bind(femb_object* o, void* dev_doubles) {
+  FEMB_TRY
+  if (!o || !dev_doubles) throw ArgError("femb_reduce_bind: NULL argument");
+  o->d_allred = static_cast<double*>(dev_doubles);
+  FEMB_CATCH
+}
+
+int femb_implicit_solve_begin(femb_object* o, float dt, int32_t method, int32_t preconditioned, int32_t max_iter,
+                              float tol) {
+  FEMB_TRY
+  check_solve_args(o, method);
+  FEMB_CUDA(cudaSetDevice(o->device));
+  o->prog.reset(new SolveProgram());
+  try {
+    build_program(o, *o->prog, dt, method, preconditioned, max_iter, tol);
+  } catch (...) {
+    o->prog.reset();
+    throw;
   }
-  launch_copy_xyz(c, nv, iv.x, o->vs.vel);          // vel = x (222-223)
-  if (iters_out || resid_out) {
-    poll(o);
-    if (iters_out) *iters_out = o->h_sc->iters;
-    if (resid_out) *resid_out = method == 1 ? (float)o->h_sc->delta_new : (float)o->h_sc->err;
+  FEMB_CATCH
+}
+
+int femb_implicit_solve_advance(femb_object* o) {
+  try {
+    if (!o) throw ArgError("NULL object");
+    if (!o->prog) throw StateError("no solve in progress: call femb_implicit_solve_begin first");
+    FEMB_CUDA(cudaSetDevice(o->device));
+    return advance(o);
+  } catch (const std::exception& ex) {
+    return femb::fail(ex);
   }
+}
+
+int femb_implicit_solve_poll(femb_object* o, int32_t* done_out, int32_t* iters_out, float* resid_out) {
+  FEMB_TRY
+  if (!o) throw ArgError("NULL object");
+  if (!o->implicit) throw StateError("object was created without implicit buffers");
+  FEMB_CUDA(cudaSetDevice(o->device));
+  poll(o);
+  if (done_out) *done_out = (o->h_sc->done | o->h_sc->terminal) != 0;
+  if (iters_out) *iters_out = o->h_sc->iters;
+  if (resid_out) *resid_out = o->last_method == 1 ? (float)o->h_sc->delta_new : (float)o->h_sc->err;
+  FEMB_CATCH
+}
+
+int femb_implicit_solve_finish(femb_object* o, int32_t* iters_out, float* resid_out) {
+  FEMB_TRY
+  if (!o) throw ArgError("NULL object");
+  if (!o->prog) throw StateError("no solve in progress");
+  FEMB_CUDA(cudaSetDevice(o->device));
+  finish(o, iters_out, resid_out);
   FEMB_CATCH
 }
 

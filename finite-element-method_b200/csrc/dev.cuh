@@ -20,6 +20,8 @@ struct DevTiling {
   int max_rounds;
   int nc;                // corners per element (dim + 1)
   int prefetch_dist;     // tiles ahead whose element planes are prefetched into L2 (0 = off)
+  const uint8_t* bskip;  // [n_boundary] multi-GPU: 1 = shared vertex counted by ANOTHER rank in global
+                         // reductions (dots, norms); nullptr on single-GPU objects
 };
 
 // Shared-memory layout of k_tile (byte offsets; every region is 16-byte aligned):

@@ -18,6 +18,11 @@ enum JacobiAction { JA_NONE = 0, JA_UPDATE = 1, JA_ACCEPT = 2, JA_REVERT = 4 };
 
 __device__ __forceinline__ float dot3(const float4& a, const float4& b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 
+// multi-GPU: vertex i (library numbering) is counted in global reductions by this rank
+__device__ __forceinline__ bool counted(const RedMask& m, int i) {
+  return m.bskip == nullptr || i < m.n_interior || m.bskip[i - m.n_interior] == 0;
+}
+
 // Sum red[0..n) in index order within each thread's strided slice, then a fixed tree.
 __device__ double final_sum(const double* red, int n) {
   __shared__ double s[256];
@@ -40,7 +45,7 @@ __global__ void k_scalars_reset(SolveScalars* sc) {
 
 // x = b ; r = rhs - op(x) ; d = r ; partial r.r        (implicit.py:313-334)
 __global__ void __launch_bounds__(256) k_cg_init(int n, ImplicitVecs iv, const float4* rhs, const float4* opx,
-                                                 double* red) {
+                                                 double* red, RedMask mask) {
   __shared__ float s_warp[32];
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   float v = 0.f;
@@ -50,7 +55,7 @@ __global__ void __launch_bounds__(256) k_cg_init(int n, ImplicitVecs iv, const f
     iv.x[i] = b;
     iv.r[i] = r;
     iv.d[i] = r;
-    v = dot3(r, r);
+    v = counted(mask, i) ? dot3(r, r) : 0.f;
   }
   const float t = block_sum(v, s_warp);
   if (threadIdx.x == 0) red[blockIdx.x] = (double)t;
@@ -66,7 +71,7 @@ __global__ void __launch_bounds__(256) k_cg_scalar(int kind, int n_red, const do
   if (kind == 0) {
     sc->delta_new = s;
     sc->iters = 0;
-    sc->done = !(0 < max_iter && (float)s > tol);
+    sc->done = !(0 < max_iter && (tol < 0.f || (float)s > tol));   // tol < 0: fixed iteration count
   } else if (kind == 1) {
     sc->dq = s;
     sc->alpha = (float)sc->delta_new / (float)s;
@@ -75,12 +80,13 @@ __global__ void __launch_bounds__(256) k_cg_scalar(int kind, int n_red, const do
     sc->delta_new = s;
     sc->beta = (float)s / (float)sc->delta_old;
     sc->iters += 1;
-    sc->done = !(sc->iters < max_iter && (float)s > tol);
+    sc->done = !(sc->iters < max_iter && (tol < 0.f || (float)s > tol));
   }
 }
 
 // x += alpha d ; r -= alpha q ; partial r.r               (implicit.py:357-381)
-__global__ void __launch_bounds__(256) k_cg_update_xr(int n, ImplicitVecs iv, double* red, const SolveScalars* sc) {
+__global__ void __launch_bounds__(256) k_cg_update_xr(int n, ImplicitVecs iv, double* red, const SolveScalars* sc,
+                                                      RedMask mask) {
   __shared__ float s_warp[32];
   if (sc->done) return;
   const float alpha = sc->alpha;
@@ -93,7 +99,7 @@ __global__ void __launch_bounds__(256) k_cg_update_xr(int n, ImplicitVecs iv, do
     r.x -= alpha * q.x; r.y -= alpha * q.y; r.z -= alpha * q.z;
     iv.x[i] = x;
     iv.r[i] = r;
-    v = dot3(r, r);
+    v = counted(mask, i) ? dot3(r, r) : 0.f;
   }
   const float t = block_sum(v, s_warp);
   if (threadIdx.x == 0) red[blockIdx.x] = (double)t;
@@ -114,7 +120,7 @@ __global__ void __launch_bounds__(256) k_cg_update_d(int n, ImplicitVecs iv, con
 
 // Jacobi control flow, implicit.py:234-261, from err = ||b - A x|| of the CURRENT iterate.
 __global__ void __launch_bounds__(256) k_jacobi_decide(int n_red, const double* red, SolveScalars* sc, float tol,
-                                                       int max_iter) {
+                                                       int max_iter, int fixed) {
   if (sc->done) return;
   if (sc->terminal) {
     if (threadIdx.x == 0) sc->done = 1;
@@ -125,6 +131,18 @@ __global__ void __launch_bounds__(256) k_jacobi_decide(int n_red, const double* 
   const float err = sqrtf((float)s);
   int action = JA_NONE;
   sc->err = err;
+  if (fixed) {                 // benchmark mode: exactly max_iter updates, no revert / early stop
+    sc->p_err = err;
+    sc->first = 0;
+    if (sc->iters < max_iter) {
+      sc->iters += 1;
+      sc->action = JA_ACCEPT | JA_UPDATE;
+    } else {
+      sc->terminal = 1;
+      sc->action = JA_ACCEPT;
+    }
+    return;
+  }
   if (sc->first) {
     sc->p_err = err;           // p_err = err (235); past_vec_x stays stale
     sc->first = 0;
@@ -259,18 +277,20 @@ void launch_scalars_reset(const LaunchCfg& c, SolveScalars* sc) {
   note_launch("scalars_reset", c.stream);
 }
 void launch_cg_init(const LaunchCfg& c, int n_vert, ImplicitVecs iv, const float4* rhs, const float4* opx,
-                    double* red, SolveScalars* sc, float tol, int max_iter) {
-  k_cg_init<<<nblk(n_vert), 256, 0, c.stream>>>(n_vert, iv, rhs, opx, red);
+                    double* red, RedMask mask) {
+  k_cg_init<<<nblk(n_vert), 256, 0, c.stream>>>(n_vert, iv, rhs, opx, red, mask);
   note_launch("cg_init", c.stream);
-  k_cg_scalar<<<1, 256, 0, c.stream>>>(0, nblk(n_vert), red, sc, tol, max_iter);
+}
+void launch_cg_delta0(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc, float tol, int max_iter) {
+  k_cg_scalar<<<1, 256, 0, c.stream>>>(0, n_red, red, sc, tol, max_iter);
   note_launch("cg_scalar0", c.stream);
 }
 void launch_cg_alpha(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc) {
   k_cg_scalar<<<1, 256, 0, c.stream>>>(1, n_red, red, sc, 0.f, 0);
   note_launch("cg_alpha", c.stream);
 }
-void launch_cg_update_xr(const LaunchCfg& c, int n_vert, ImplicitVecs iv, double* red, SolveScalars* sc) {
-  k_cg_update_xr<<<nblk(n_vert), 256, 0, c.stream>>>(n_vert, iv, red, sc);
+void launch_cg_update_xr(const LaunchCfg& c, int n_vert, ImplicitVecs iv, double* red, SolveScalars* sc, RedMask mask) {
+  k_cg_update_xr<<<nblk(n_vert), 256, 0, c.stream>>>(n_vert, iv, red, sc, mask);
   note_launch("cg_update_xr", c.stream);
 }
 void launch_cg_beta(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc, float tol, int max_iter) {
@@ -282,8 +302,8 @@ void launch_cg_update_d(const LaunchCfg& c, int n_vert, ImplicitVecs iv, const S
   note_launch("cg_update_d", c.stream);
 }
 void launch_jacobi_decide(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc, float tol,
-                          int max_iter) {
-  k_jacobi_decide<<<1, 256, 0, c.stream>>>(n_red, red, sc, tol, max_iter);
+                          int max_iter, int fixed) {
+  k_jacobi_decide<<<1, 256, 0, c.stream>>>(n_red, red, sc, tol, max_iter, fixed);
   note_launch("jacobi_decide", c.stream);
 }
 void launch_jacobi_update(const LaunchCfg& c, int n_vert, ImplicitVecs iv, SolveScalars* sc) {

@@ -85,14 +85,21 @@ void launch_apply(int dim, const LaunchCfg& c, const DevTiling& tl, Planes h, Ve
 int reduce_slots(const DevTiling& tl, const LaunchCfg& c);  // doubles needed in a reduction buffer
 
 // CG / Jacobi vector kernels (all early-exit on sc->done)
+struct RedMask {           // which vertices this rank counts in global reductions (multi-GPU owner mask)
+  int n_interior;
+  const uint8_t* bskip;    // nullptr: count every vertex
+};
+// x = b, r = rhs - opx, d = r, per-CTA partials of r.r -> red[0 .. ceil(n_vert/256))
 void launch_cg_init(const LaunchCfg& c, int n_vert, ImplicitVecs iv, const float4* rhs, const float4* opx,
-                    double* red, SolveScalars* sc, float tol, int max_iter);
+                    double* red, RedMask mask);
+// delta_new = sum red[0..n_red), loop entry test
+void launch_cg_delta0(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc, float tol, int max_iter);
 void launch_cg_alpha(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc);
-void launch_cg_update_xr(const LaunchCfg& c, int n_vert, ImplicitVecs iv, double* red, SolveScalars* sc);
+void launch_cg_update_xr(const LaunchCfg& c, int n_vert, ImplicitVecs iv, double* red, SolveScalars* sc, RedMask mask);
 void launch_cg_beta(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc, float tol, int max_iter);
 void launch_cg_update_d(const LaunchCfg& c, int n_vert, ImplicitVecs iv, const SolveScalars* sc);
 void launch_jacobi_decide(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc, float tol,
-                          int max_iter);
+                          int max_iter, int fixed);
 void launch_jacobi_update(const LaunchCfg& c, int n_vert, ImplicitVecs iv, SolveScalars* sc);
 void launch_scalars_reset(const LaunchCfg& c, SolveScalars* sc);
 

@@ -2,6 +2,8 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <functional>
+#include <memory>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -37,6 +39,22 @@ struct StepGraph {          // cached CUDA graph of n fused explicit steps
   uint64_t launches = 0;
 };
 
+// The implicit solve as a list of device-work segments separated by communication points, so that
+// the same code drives the single-GPU solve (no communication) and the slab-partitioned solve, where
+// the caller (one process per GPU) performs the halo exchange / allreduce between segments.
+struct SolveOp {
+  std::function<void()> run;
+  int comm;                 // femb_comm the caller must perform AFTER this op (0 = none)
+};
+struct SolveProgram {
+  std::vector<SolveOp> prologue, iteration;
+  size_t pc = 0;
+  bool in_prologue = true;
+  int iters_issued = 0;
+  int method = 0, max_iter = 0;
+  bool fixed = false;
+};
+
 }  // namespace femb
 
 struct femb_object {
@@ -66,6 +84,9 @@ struct femb_object {
   bool own_stream = false;
   femb::LaunchCfg cfg{};
   femb::StepGraph graph;
+  std::unique_ptr<femb::SolveProgram> prog;   // implicit solve in progress (begin/advance/finish)
+  int last_method = 1;              // method of the most recent solve (what `resid` means)
+  double* d_allred = nullptr;       // multi-GPU: caller-owned device doubles the caller sum-allreduces
   femb::Halo halo;                  // multi-GPU: vertices shared with neighbouring ranks
   bool halo_dirty = false;          // remote partial slots hold data of an earlier exchange
   // every un-phased pass on a halo object must see zeros in the remote slots

@@ -240,6 +240,7 @@ __global__ void __launch_bounds__(kBoundaryBlock) k_boundary(DevTiling tl, typen
     }
     const int gid = tl.n_interior + b;
     Op::vertex(a, gid, Op::load_vertex(a, gid), Op::pre(a, gid), acc, red);
+    if (Op::REDUCE && tl.bskip && tl.bskip[b]) red = 0.f;   // shared vertex owned by the neighbouring rank
   }
   if (Op::REDUCE) {
     const float r = block_sum(red, s_warp);

@@ -19,11 +19,15 @@ CSRC = os.path.join(os.path.dirname(_HERE), "csrc")
 # femb_field
 F_POS, F_VEL, F_VEL_G, F_FORCE, F_GRAD, F_MASS, F_REF_POS, F_VEC_B, F_VEC_X, F_PAST_X, F_DIAG_A = range(11)
 F_ELEM_VOLUME, F_ELEM_REF, F_ELEM_PHI, F_ELEM_H = 32, 33, 34, 35
+# femb_comm
+COMM_NONE, COMM_HALO, COMM_ALLREDUCE, COMM_ITER = 0, 1, 2, 3
 
 EXPORTS = [
     "femb_object_create", "femb_object_destroy", "femb_object_info", "femb_set_stream", "femb_blocks_set",
     "femb_explicit_grad", "femb_energy_grad", "femb_kinematic", "femb_explicit_step", "femb_explicit_step_timed", "femb_implicit_solve",
     "femb_halo_bind", "femb_halo_mass", "femb_explicit_step_phase",
+    "femb_reduce_bind", "femb_implicit_solve_begin", "femb_implicit_solve_advance", "femb_implicit_solve_poll",
+    "femb_implicit_solve_finish",
     "femb_advect_implicit", "femb_implicit_assemble", "femb_implicit_apply", "femb_get", "femb_set",
     "femb_get_energy", "femb_sync", "femb_last_error", "femb_launch_count", "femb_version",
     "femb_tiling_build", "femb_tiling_destroy", "femb_tiling_info", "femb_tiling_get",
@@ -38,6 +42,7 @@ class Desc(C.Structure):
         ("rho", C.c_float), ("mu", C.c_float), ("lam", C.c_float), ("damping", C.c_float),
         ("implicit", C.c_int32), ("tile_elems", C.c_int32), ("device", C.c_int32),
         ("n_halo", C.c_int32), ("halo_verts", C.POINTER(C.c_int32)),
+        ("halo_owned", C.POINTER(C.c_uint8)),
     ]
 
 
@@ -85,6 +90,11 @@ def lib():
         "femb_halo_mass": (C.c_int, [vp, i32]),
         "femb_explicit_step_phase": (C.c_int, [vp, f32, fp, i32]),
         "femb_implicit_solve": (C.c_int, [vp, f32, i32, i32, i32, f32, ip, fp]),
+        "femb_reduce_bind": (C.c_int, [vp, vp]),
+        "femb_implicit_solve_begin": (C.c_int, [vp, f32, i32, i32, i32, f32]),
+        "femb_implicit_solve_advance": (C.c_int, [vp]),
+        "femb_implicit_solve_poll": (C.c_int, [vp, ip, ip, fp]),
+        "femb_implicit_solve_finish": (C.c_int, [vp, ip, fp]),
         "femb_advect_implicit": (C.c_int, [vp, f32, fp]),
         "femb_implicit_assemble": (C.c_int, [vp, f32]),
         "femb_implicit_apply": (C.c_int, [vp, f32, i32, fp, fp]),
@@ -131,9 +141,14 @@ class Handle:
     """Owns one femb_object."""
 
     def __init__(self, verts, elems, center, rho, mu, lam, damping, implicit=False, tile_elems=0, device=-1,
-                 halo_verts=None):
+                 halo_verts=None, halo_owned=None):
         halo = np.ascontiguousarray(halo_verts if halo_verts is not None else [], dtype=np.int32)
         self.n_halo = int(halo.size)
+        owned = None
+        if halo_owned is not None:
+            owned = np.ascontiguousarray(halo_owned, dtype=np.uint8)
+            if owned.size != halo.size:
+                raise ValueError("halo_owned must have one entry per halo vertex")
         verts = np.ascontiguousarray(verts, dtype=np.float32)
         elems = np.ascontiguousarray(elems, dtype=np.int32)
         self.dim = int(verts.shape[1])
@@ -149,6 +164,7 @@ class Handle:
         d.rho, d.mu, d.lam, d.damping = float(rho), float(mu), float(lam), float(damping)
         d.implicit, d.tile_elems, d.device = int(bool(implicit)), int(tile_elems), int(device)
         d.n_halo, d.halo_verts = self.n_halo, _iptr(halo)
+        d.halo_owned = owned.ctypes.data_as(C.POINTER(C.c_uint8)) if owned is not None else None
         self._h = C.c_void_p()
         check(lib().femb_object_create(C.byref(d), C.byref(self._h)))
 
@@ -247,6 +263,35 @@ class Handle:
             return it.value, res.value
         check(lib().femb_implicit_solve(self._h, float(dt), int(method), int(preconditioned), int(max_iter),
                                         float(tol), None, None))
+
+    # -- the solve as segments between communication points (multi-GPU callers own the collectives)
+    def reduce_bind(self, dev_ptr):
+        check(lib().femb_reduce_bind(self._h, C.c_void_p(int(dev_ptr))))
+
+    def solve_begin(self, dt, method, preconditioned, max_iter=0, tol=-1.0):
+        check(lib().femb_implicit_solve_begin(self._h, float(dt), int(method), int(preconditioned), int(max_iter),
+                                              float(tol)))
+
+    def solve_advance(self):
+        rc = lib().femb_implicit_solve_advance(self._h)
+        if rc < 0:
+            check(rc)
+        return rc
+
+    def solve_poll(self):
+        done, it, res = C.c_int32(), C.c_int32(), C.c_float()
+        check(lib().femb_implicit_solve_poll(self._h, C.byref(done), C.byref(it), C.byref(res)))
+        return bool(done.value), it.value, res.value
+
+    def last_solve_iters(self):
+        return self.solve_poll()[1]
+
+    def solve_finish(self, fetch=True):
+        if fetch:
+            it, res = C.c_int32(), C.c_float()
+            check(lib().femb_implicit_solve_finish(self._h, C.byref(it), C.byref(res)))
+            return it.value, res.value
+        check(lib().femb_implicit_solve_finish(self._h, None, None))
 
     def advect_implicit(self, dt, g_dir):
         g = gvec(g_dir, self.dim)

@@ -26,6 +26,13 @@ def slab_halo_vertices(rank, world, local_layers, ny, nz):
     return np.concatenate([left, right]), left.size, right.size
 
 
+def slab_halo_owned(rank, world, local_layers, ny, nz):
+    """Per halo vertex (order of slab_halo_vertices): 1 if THIS rank counts it in global reductions.
+    A shared plane belongs to the LEFT rank, so a rank owns its right plane and not its left one."""
+    _, nl, nr = slab_halo_vertices(rank, world, local_layers, ny, nz)
+    return np.concatenate([np.zeros(nl, np.uint8), np.ones(nr, np.uint8)])
+
+
 def owner_mask(rank, world, local_layers, ny, nz):
     """1.0 for vertices this rank counts in global reductions (a shared plane belongs to the LEFT rank)."""
     plane = (ny + 1) * (nz + 1)
@@ -41,6 +48,8 @@ class SlabHalo:
     def __init__(self, rank, world, local_layers, ny, nz):
         self.rank, self.world = rank, world
         self.vertex_ids, self.n_left, self.n_right = slab_halo_vertices(rank, world, local_layers, ny, nz)
+        self.owned = slab_halo_owned(rank, world, local_layers, ny, nz)
+        self.allred = None
         self.n = int(self.vertex_ids.size)
         self.send = self.recv = None
         self._graphs = {}
@@ -54,6 +63,8 @@ class SlabHalo:
         self.send = torch.zeros((self.n, 4), dtype=torch.float32, device=device or "cuda")
         self.recv = torch.zeros((self.n, 4), dtype=torch.float32, device=device or "cuda")
         handle.halo_bind(self.send.data_ptr(), self.recv.data_ptr())
+        self.allred = torch.zeros(1, dtype=torch.float64, device=device or "cuda")
+        handle.reduce_bind(self.allred.data_ptr())
         handle.halo_mass(1)
         self.exchange()
         handle.halo_mass(2)
@@ -102,3 +113,97 @@ class SlabHalo:
             self.captured_launches = getattr(self, "captured_launches", 0) + g[1]
         g[0].replay()
         self.replayed_launches = getattr(self, "replayed_launches", 0) + g[1]
+
+    # ---- implicit solve: the library enqueues device work up to a communication point, we communicate
+    def allreduce(self):
+        """Sum of the bound scalar over all ranks (identical bits on every rank, so the device-side
+        convergence flags never diverge between ranks)."""
+        import torch.distributed as dist
+
+        dist.all_reduce(self.allred, op=dist.ReduceOp.SUM)
+
+    def _until_iter(self, handle):
+        """Advance to the end of the prologue / of one solver iteration."""
+        from . import _capi
+
+        n = 0
+        while True:
+            k = handle.solve_advance()
+            n += 1
+            if k == _capi.COMM_HALO:
+                self.exchange()
+            elif k == _capi.COMM_ALLREDUCE:
+                self.allreduce()
+            elif k == _capi.COMM_ITER:
+                return n
+            else:
+                raise RuntimeError("unexpected communication request %r" % (k,))
+
+    def implicit_solve(self, handle, dt, method, preconditioned, max_iter=0, tol=-1.0, use_graph=True, fetch=True):
+        """implicit_solver_neo_hookean (implicit.py:201-223) on a slab-partitioned mesh: halo sums after every
+        operator pass, one scalar allreduce per dot product.  One iteration (kernels + NCCL) is captured
+        into a CUDA graph and replayed; convergence is polled every few iterations."""
+        from . import _capi
+
+        fixed = (tol == 0.0)
+        n_cap = max_iter if max_iter > 0 else (500 if method == 1 else 20000)
+        n_it = n_cap if method == 1 else n_cap + 2
+        handle.solve_begin(dt, method, preconditioned, max_iter, tol)
+        self._until_iter(handle)                       # prologue: assemble, A^T b, initial residual
+        graph = None
+        if use_graph and n_it >= 4 and self.send.is_cuda:
+            torch = self.torch
+            key = ("solve", float(dt), int(method), int(preconditioned), int(max_iter), float(tol))
+            graph = self._graphs.get(key)
+            if graph is None:
+                self._until_iter(handle)               # iteration 1 runs eagerly (warms NCCL for these sizes)
+                n_it -= 1
+                torch.cuda.current_stream().synchronize()
+                g = torch.cuda.CUDAGraph()
+                before = _capi.launch_count()
+                with torch.cuda.graph(g, stream=torch.cuda.current_stream(), capture_error_mode="thread_local"):
+                    self._until_iter(handle)           # captured, not executed
+                graph = self._graphs[key] = (g, _capi.launch_count() - before)
+        it, chunk = 0, 4
+        while it < n_it:
+            n = n_it - it if fixed else min(chunk, n_it - it)
+            for _ in range(n):
+                if graph is not None:
+                    graph[0].replay()
+                    self.replayed_launches = getattr(self, "replayed_launches", 0) + graph[1]
+                else:
+                    self._until_iter(handle)
+            it += n
+            if not fixed:
+                done, _, _ = handle.solve_poll()
+                if done:
+                    break
+                chunk = min(chunk * 2, 32)
+        return handle.solve_finish(fetch)
+
+    def close(self):
+        """Drop the captured CUDA graphs (they hold NCCL work: the process group cannot be destroyed while
+        they are alive)."""
+        self._graphs.clear()
+        if self.send is not None and self.send.is_cuda:
+            self.torch.cuda.synchronize()
+
+
+def shutdown(halo=None, timeout=20.0):
+    """Release the graphs, then destroy the process group; if NCCL teardown stalls (seen with graph-captured
+    collectives), leave after `timeout` seconds -- all results have been produced by then."""
+    import os
+    import sys
+    import threading
+
+    import torch.distributed as dist
+
+    if halo is not None:
+        halo.close()
+    sys.stdout.flush()
+    sys.stderr.flush()
+    t = threading.Timer(timeout, lambda: os._exit(0))
+    t.daemon = True
+    t.start()
+    dist.destroy_process_group()
+    t.cancel()

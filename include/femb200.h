@@ -76,6 +76,9 @@ typedef struct femb_desc {
    * (single device, main.py:40). */
   int32_t n_halo;
   const int32_t *halo_verts; /* [n_halo] original vertex ids */
+  /* [n_halo] 1 = THIS rank counts the shared vertex in global reductions (CG dots, residual norms),
+   * 0 = the neighbour does.  NULL = count all (single rank). */
+  const uint8_t *halo_owned;
 } femb_desc;
 
 typedef struct femb_info {
@@ -137,6 +140,26 @@ int femb_implicit_solve(femb_object *obj, float dt, int32_t method, int32_t prec
                         int32_t max_iter, float tol, int32_t *iters_out, float *resid_out);
 /* advect_implicit(obj, circle_blocks), implicit.py:407-437 */
 int femb_advect_implicit(femb_object *obj, float dt, const float *g_dir);
+
+/* The same solve for a caller that owns the collectives (multi-GPU slabs, one process per GPU; new --
+ * the reference is single-device).  _begin builds the solve; every _advance enqueues device work up to
+ * the next communication point and returns (>= 0) what the caller must do before advancing again:
+ *   FEMB_COMM_HALO       exchange the bound halo buffers (send -> the neighbour's recv),
+ *   FEMB_COMM_ALLREDUCE  sum-allreduce the double bound with femb_reduce_bind,
+ *   FEMB_COMM_ITER       nothing: the prologue / one solver iteration is fully enqueued; the caller may
+ *                        _poll the convergence state, then _advance into the next iteration or _finish.
+ * The sequence of return values of one iteration never changes, so a caller may capture one iteration
+ * (kernels + collectives) in a CUDA graph and replay it.  Negative return = femb_status error. */
+typedef enum femb_comm { FEMB_COMM_NONE = 0, FEMB_COMM_HALO = 1, FEMB_COMM_ALLREDUCE = 2, FEMB_COMM_ITER = 3 } femb_comm;
+int femb_reduce_bind(femb_object *obj, void *dev_double); /* caller-owned DEVICE double[1] */
+int femb_implicit_solve_begin(femb_object *obj, float dt, int32_t method, int32_t preconditioned,
+                              int32_t max_iter, float tol);
+int femb_implicit_solve_advance(femb_object *obj);
+/* synchronises; done != 0 once the loop test of implicit.py:252 / :341 has failed.  Also valid after the
+ * solve has ended (state of the most recent solve). */
+int femb_implicit_solve_poll(femb_object *obj, int32_t *done_out, int32_t *iters_out, float *resid_out);
+/* vel = x (implicit.py:222-223); ends the solve */
+int femb_implicit_solve_finish(femb_object *obj, int32_t *iters_out, float *resid_out);
 /* Pieces of the solve, exposed for parity tests: assemble H_e, b, diag(A) */
 int femb_implicit_assemble(femb_object *obj, float dt);
 /* out = A in (transpose==0) or A^T in (transpose!=0); host vectors [n_vert*dim] */

@@ -29,7 +29,8 @@ def main():
     i0, i1 = fdist.slab_range(nx, rank, world)
     verts, tets = meshgen.kuhn_box(nx, ny, nz, hh, x_cells=(i0, i1))
     halo = fdist.SlabHalo(rank, world, i1 - i0, ny, nz)
-    h = c.Handle(verts, tets, center, 1000.0, mu, lam, 10.0, tile_elems=96, halo_verts=halo.vertex_ids)
+    h = c.Handle(verts, tets, center, 1000.0, mu, lam, 10.0, implicit=True, tile_elems=96, halo_verts=halo.vertex_ids,
+                 halo_owned=halo.owned)
     h.set_stream(stream.cuda_stream)
     halo.attach(h)
     h.set(c.F_POS, gpos[i0 * plane:(i1 + 1) * plane])
@@ -38,11 +39,24 @@ def main():
     halo.explicit_steps(h, dt, g, 12, use_graph=True)     # CUDA-graph path (kernels + NCCL P2P)
     torch.cuda.synchronize()
     mine = dict(pos=h.get(c.F_POS), vel=h.get(c.F_VEL), mass=h.get(c.F_MASS), i0=i0, i1=i1)
+    # ---- implicit path on the slabs: every solver, eager and graph-replayed, then advect
+    sl_me = slice(i0 * plane, (i1 + 1) * plane)
+    gvel = (0.05 * np.random.default_rng(1).uniform(-1, 1, gpos.shape)).astype(np.float32)
+    SOLVES = [("cg", 1, 0, 1e-4, False), ("cg_ata", 1, 1, 5e-4, True), ("jacobi", 0, 0, 1e-4, True)]
+    for name, method, pre, sdt, use_graph in SOLVES:
+        h.set(c.F_POS, gpos[sl_me])
+        h.set(c.F_VEL, gvel[sl_me])
+        h.set(c.F_VEL_G, np.zeros_like(gvel[sl_me]))
+        for _ in range(2):      # second solve replays the cached graph
+            it, res = halo.implicit_solve(h, sdt, method, pre, use_graph=use_graph)
+            h.advect_implicit(sdt, g)
+        torch.cuda.synchronize()
+        mine[name] = dict(vel=h.get(c.F_VEL), pos=h.get(c.F_POS), b=h.get(c.F_VEC_B), it=it, res=res)
     allr = [None] * world
     dist.all_gather_object(allr, mine)
     ok = True
     if rank == 0:
-        hs = c.Handle(gverts, gtets, center, 1000.0, mu, lam, 10.0, tile_elems=96)
+        hs = c.Handle(gverts, gtets, center, 1000.0, mu, lam, 10.0, implicit=True, tile_elems=96)
         hs.set(c.F_POS, gpos)
         hs.explicit_step(dt, g, n)
         want_p, want_v, want_m = hs.get(c.F_POS), hs.get(c.F_VEL), hs.get(c.F_MASS)
@@ -59,9 +73,32 @@ def main():
                     if not np.array_equal(d[name][-plane:], nxt[name][:plane]):
                         ok = False
                         print("shared plane differs between ranks", r, r + 1, name)
+        for name, method, pre, sdt, _ in SOLVES:
+            hs.set(c.F_POS, gpos)
+            hs.set(c.F_VEL, gvel)
+            hs.set(c.F_VEL_G, np.zeros_like(gvel))
+            for _ in range(2):
+                it1, res1 = hs.implicit_solve(sdt, method, pre)
+                hs.advect_implicit(sdt, g)
+            want = dict(vel=hs.get(c.F_VEL), pos=hs.get(c.F_POS), b=hs.get(c.F_VEC_B))
+            for r, d in enumerate(allr):
+                sl = slice(d["i0"] * plane, (d["i1"] + 1) * plane)
+                for f, tol in (("b", 1e-4), ("vel", 2e-3), ("pos", 1e-6)):   # second step: b inherits the solver tolerance
+                    err = np.linalg.norm(d[name][f] - want[f][sl]) / np.linalg.norm(want[f][sl])
+                    if not err <= tol:
+                        ok = False
+                        print("solve", name, "rank", r, f, "rel err", err)
+                if d[name]["it"] != allr[0][name]["it"]:
+                    ok = False
+                    print("solve", name, "iteration counts differ between ranks")
+                if r + 1 < world and not np.array_equal(d[name]["vel"][-plane:], allr[r + 1][name]["vel"][:plane]):
+                    ok = False
+                    print("solve", name, "shared plane velocity differs between ranks", r, r + 1)
+            print("solve", name, "iters slab/single", allr[0][name]["it"], it1, "resid", allr[0][name]["res"], res1)
         print("SLAB_OK" if ok else "SLAB_FAIL")
+    halo.close()
     h.close()
-    dist.destroy_process_group()
+    fdist.shutdown()
 
 
 if __name__ == "__main__":

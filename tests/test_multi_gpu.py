@@ -72,6 +72,93 @@ def test_halo_exchange_pattern_gloo_world2():
     assert res == [(0, True), (1, True)]
 
 
+class _FakeHandle:
+    """Scripted stand-in for the library's solve state machine (femb_implicit_solve_begin/_advance/...):
+    the same communication requests in the same order, with host tensors, so the driver logic of
+    SlabHalo.implicit_solve runs under gloo without a GPU."""
+
+    PROLOGUE = [1, 2, 3]            # HALO, ALLREDUCE, ITER
+    ITERATION = [1, 1, 2, 2, 3]     # A^T A-CG: two operator passes, two dots
+
+    def __init__(self, halo, rank, stop_after):
+        self.halo, self.rank, self.stop_after = halo, rank, stop_after
+        self.script, self.pc, self.iters, self.log = None, 0, 0, []
+        self.pending = None
+
+    def solve_begin(self, dt, method, pre, max_iter, tol):
+        self.script, self.pc, self.iters = self.PROLOGUE, 0, 0
+
+    def _consume(self):
+        if self.pending == 1:
+            self.log.append(("halo", self.halo.recv.clone()))
+        elif self.pending == 2:
+            self.log.append(("sum", float(self.halo.allred[0])))
+        self.pending = None
+
+    def solve_advance(self):
+        self._consume()
+        k = self.script[self.pc]
+        self.pc += 1
+        if k == 1:
+            self.halo.send[:] = float(10 * self.iters + self.rank + 1)
+        elif k == 2:
+            self.halo.allred[0] = float(self.rank + 1 + self.iters)
+        elif k == 3:
+            if self.script is self.ITERATION:
+                self.iters += 1
+            self.script, self.pc = self.ITERATION, 0
+        self.pending = k
+        return k
+
+    def solve_poll(self):
+        return self.iters >= self.stop_after, self.iters, 0.0
+
+    def solve_finish(self, fetch=True):
+        self._consume()
+        return self.iters, 0.0
+
+
+def _gloo_solve_worker(rank, world, port, q):
+    import torch
+    import torch.distributed as dist
+
+    sys.path[:0] = [os.path.join(ROOT, "finite-element-method_b200"), ROOT]
+    from femb200 import dist as fdist
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    halo = fdist.SlabHalo(rank, world, 3, 2, 2)
+    halo.send, halo.recv = torch.zeros((halo.n, 4)), torch.zeros((halo.n, 4))
+    halo.allred = torch.zeros(1, dtype=torch.float64)
+    fh = _FakeHandle(halo, rank, stop_after=10)
+    iters, _ = halo.implicit_solve(fh, 1e-4, 1, 1, max_iter=50, tol=1e-5)
+    other = 1 - rank
+    ok = iters == 12                      # polled after 4 (not done) and after 4 + 8 (done): chunks double
+    sums = [v for k, v in fh.log if k == "sum"]
+    halos = [v for k, v in fh.log if k == "halo"]
+    ok &= len(sums) == 1 + 2 * iters and len(halos) == 1 + 2 * iters
+    ok &= sums[0] == 3.0 and all(s == 3.0 + 2 * (i // 2) for i, s in enumerate(sums[1:]))
+    ok &= all(bool((hv == hv[0, 0]).all()) for hv in halos)
+    ok &= float(halos[0][0, 0]) == other + 1 and float(halos[-1][0, 0]) == 10 * (iters - 1) + other + 1
+    q.put((rank, bool(ok), iters))
+    dist.destroy_process_group()
+
+
+def test_implicit_solve_driver_gloo_world2():
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 31500 + os.getpid() % 2000
+    procs = [ctx.Process(target=_gloo_solve_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+    assert res == [(0, True, 12), (1, True, 12)], res
+
+
 @pytest.mark.gpu
 def test_two_rank_slabs_match_single_gpu():
     import torch
@@ -80,5 +167,5 @@ def test_two_rank_slabs_match_single_gpu():
         pytest.skip("needs 2 GPUs")
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
                         "--master-addr", "127.0.0.1", "--master-port", "29611",
-                        os.path.join(ROOT, "tests", "mp_slab_check.py")], capture_output=True, text=True, timeout=600)
+                        os.path.join(ROOT, "tests", "mp_slab_check.py")], capture_output=True, text=True, timeout=180)
     assert "SLAB_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
