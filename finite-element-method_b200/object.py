@@ -52,6 +52,13 @@ class Object:
             self.vec_b = fields.VertexField(self, _capi.F_VEC_B, writable=False)
             self.vec_x = fields.VertexField(self, _capi.F_VEC_X)
             self.past_vec_x = fields.VertexField(self, _capi.F_PAST_X)
+        # extension (synthetic benchmark meshes): initial state x = X + jitter * h * U(-1, 1)
+        if config.get('jitter'):
+            rng = np.random.default_rng(config.get('seed', 0))
+            h = config.get('h') or (config.get('side_length', 1.0) / max(config.get('subdivisions', 1), 1))
+            jit = rng.uniform(-1.0, 1.0, vertices.shape).astype(np.float32)
+            pos = (vertices + self.center[None, :].astype(np.float32)).astype(np.float32)
+            self._h.set(_capi.F_POS, pos + np.float32(config.get('jitter') * h) * jit)
         self._pending_grad = False   # neo_hookean_1_grad requested, not yet materialised
         self._force_clean = True     # particles.force is known to be all zero
         self._blocks_seen = None
@@ -114,6 +121,18 @@ class Object:
                 f.write('v {:.8f} {:.8f} {:.8f}\n'.format(*(list(p) + [0.0])[:3]))
             for t in remap[faces] + 1:
                 f.write('f {} {} {}\n'.format(*t))
+
+    def count_inverted(self, pos=None):
+        """Number of elements with det F <= 0 (the explicit kernel takes log(det F) unclamped,
+        explicit.py:24-25, so these produce NaN): sign(det Ds) != sign(det Dm)."""
+        pos = self.particles.pos.to_numpy() if pos is None else pos
+        ref = self.particles.ref_pos.to_numpy()
+        el = self.elements.vertex_indices.to_numpy()
+
+        def dets(p):
+            e = (p[el[:, 1:]] - p[el[:, :1]]).astype(np.float64)
+            return np.linalg.det(e)
+        return int((dets(pos) * dets(ref) <= 0).sum())
 
     def sync(self):
         self._h.sync()
