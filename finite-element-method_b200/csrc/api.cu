@@ -107,8 +107,23 @@ int femb_object_create(const femb_desc* d, femb_object** out) {
       if (!vec.empty())
         FEMB_CUDA(cudaMemcpyAsync(dst, vec.data(), vec.size() * sizeof(T_), cudaMemcpyHostToDevice, o->stream));
     };
-    TileDesc* d_tiles; LocalVert* d_lv; uint16_t* d_jds; uint32_t* d_rounds; int32_t* d_bptr;
-    upload(d_tiles, t.tiles);
+    DevTile* d_tiles; LocalVert* d_lv; uint16_t* d_jds; uint32_t* d_rounds; int32_t* d_bptr;
+    // CTAs of the tile kernels resident at once
+    const int occ = std::max(1, std::min(std::min(2048 / kBlock, kMinCtas), (227 * 1024) / (tile_smem_bytes(t) + 1024)));
+    const int grid = std::min(t.n_tiles, prop.multiProcessorCount * occ);
+    std::vector<DevTile> dev_tiles((size_t)t.n_tiles);
+    for (int i = 0; i < t.n_tiles; ++i) {
+      const TileDesc& s = t.tiles[i];
+      DevTile& q = dev_tiles[i];
+      q = DevTile{s.slot_off, s.n_elem, s.lv_off, s.n_lv, s.jds_off, s.rounds_off, s.n_rounds, s.n_int, s.int_base,
+                  0, 0, 0, 0, 0, 0, 0};
+      if (i + grid < t.n_tiles) {
+        const TileDesc& n = t.tiles[i + grid];
+        q.nx_slot_off = n.slot_off; q.nx_n_elem = n.n_elem; q.nx_lv_off = n.lv_off; q.nx_n_lv = n.n_lv;
+        q.nx_jds_off = n.jds_off; q.nx_int_base = n.int_base; q.nx_n_int = n.n_int;
+      }
+    }
+    upload(d_tiles, dev_tiles);
     upload(d_lv, t.lv);
     upload(d_jds, t.jds);
     upload(d_rounds, t.rounds);
@@ -128,11 +143,9 @@ int femb_object_create(const femb_desc* d, femb_object** out) {
       for (int k = 0; k < d->n_halo; ++k) bskip[t.halo_b[k]] = d->halo_owned[k] ? 0 : 1;
       upload(d_bskip, bskip);
     }
-    // CTAs of the tile kernels resident at once = how far ahead the L2 prefetch looks
-    const int occ = std::max(1, std::min(2048 / kBlock, (227 * 1024) / (tile_smem_bytes(t) + 1024)));
     o->dtl = DevTiling{d_tiles, d_lv, d_jds, d_rounds, d_bptr, t.n_tiles, t.n_interior, t.n_boundary, t.n_vert,
                        t.n_slots, (t.max_tile_elems + 31) / 32 * 32, t.max_lv, (t.max_rounds + 3) / 4 * 4, t.nc,
-                       prop.multiProcessorCount * occ, d_bskip};
+                       prop.multiProcessorCount * occ, grid, d_bskip};
 
     const size_t ns = (size_t)t.n_slots, nv = (size_t)t.n_vert;
     o->e.p0 = o->alloc<float4>(ns);
@@ -253,7 +266,7 @@ int femb_energy_grad(femb_object* o, float* U_out) {
   o->prep_full_pass();
   launch_explicit(o->dim, EX_ENERGY, o->cfg, o->dtl, o->e, o->vs, o->mat, KinArgs{}, o->d_phi, o->d_red);
   const int nbb = (o->dtl.n_boundary + 255) / 256;
-  launch_reduce_final(o->cfg, o->dtl.n_tiles + nbb, o->d_red, o->d_U);
+  launch_reduce_final(o->cfg, energy_tile_grid(o->dtl) + nbb, o->d_red, o->d_U);
   if (U_out) return femb_get_energy(o, U_out);
   FEMB_CATCH
 }

@@ -26,7 +26,7 @@ int fail(const std::exception& ex);
   }                                  \
   return FEMB_OK;
 
-static int apply_red_slots(const femb_object* o) { return o->dtl.n_tiles + (o->dtl.n_boundary + 255) / 256; }
+static int apply_red_slots(const femb_object* o) { return apply_tile_grid(o->dtl) + (o->dtl.n_boundary + 255) / 256; }
 
 static void poll(femb_object* o) {
   FEMB_CUDA(cudaMemcpyAsync(o->h_sc, o->d_sc, sizeof(SolveScalars), cudaMemcpyDeviceToHost, o->stream));

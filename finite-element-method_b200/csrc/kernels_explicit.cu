@@ -64,6 +64,7 @@ __device__ __forceinline__ void kinematic_update(float4& p, float4& v, const flo
 // ---------------------------------------------------------------------------
 template <int D>
 struct OpSetup {
+  static constexpr bool PERSIST = false;
   static constexpr int BLOCK = kBlock, MIN_CTAS = kMinCtas,NSTAGE = 1, GATHER = G_UNIFORM;
   static constexpr bool REDUCE = false;
   struct Args {
@@ -149,6 +150,7 @@ struct OpSetup {
 // ---------------------------------------------------------------------------
 template <int D, int MODE>
 struct OpExplicit {
+  static constexpr bool PERSIST = FEMB_PERSIST_EXPLICIT != 0;
   static constexpr int BLOCK = kBlock, MIN_CTAS = kMinCtas,NSTAGE = D * D, GATHER = G_STAR;
   static constexpr bool REDUCE = (MODE == EX_ENERGY);
   struct Args {
@@ -327,6 +329,8 @@ void launch_explicit(int dim, int mode, const LaunchCfg& c, const DevTiling& tl,
 #undef FEMB_CASE
   throw std::runtime_error("launch_explicit: bad dim/mode");
 }
+
+int energy_tile_grid(const DevTiling& tl) { return tile_grid<OpExplicit<3, EX_ENERGY>>(tl); }
 
 void launch_kinematic(int dim, const LaunchCfg& c, int n_vert, VertexState vs, KinArgs kin, int use_grad) {
   const int nb = (n_vert + 255) / 256;

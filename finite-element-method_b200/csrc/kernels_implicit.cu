@@ -17,6 +17,7 @@ namespace femb {
 // ---------------------------------------------------------------------------
 template <int D>
 struct OpAssemble {
+  static constexpr bool PERSIST = FEMB_PERSIST_ASSEMBLE != 0;
   static constexpr int BLOCK = kBlock, MIN_CTAS = kMinCtas,NSTAGE = D * D, GATHER = G_STAR;
   static constexpr bool REDUCE = false;
   struct Args {
@@ -113,6 +114,7 @@ struct OpAssemble {
 // diag(A)_{v,k} = 1 - dt^2/m_v sum_e c_{e,v} H_e[k,k]; c = dim at local vertex 0
 template <int D>
 struct OpDiag {
+  static constexpr bool PERSIST = FEMB_PERSIST_APPLY != 0;
   static constexpr int BLOCK = kBlock, MIN_CTAS = kMinCtas,NSTAGE = D, GATHER = G_UNIFORM;
   static constexpr bool REDUCE = false;
   struct Args {
@@ -150,6 +152,7 @@ struct OpDiag {
 // ---------------------------------------------------------------------------
 template <int D, int TR>
 struct OpApply {
+  static constexpr bool PERSIST = FEMB_PERSIST_APPLY != 0;
   static constexpr int BLOCK = kBlock, MIN_CTAS = kMinCtas,NSTAGE = D * D, GATHER = G_STAR;
   static constexpr bool REDUCE = true;
   struct Args {
@@ -268,10 +271,12 @@ void launch_apply(int dim, const LaunchCfg& c, const DevTiling& tl, Planes h, Ve
   }
 }
 
+int apply_tile_grid(const DevTiling& tl) { return tile_grid<OpApply<3, 0>>(tl); }
+
 int reduce_slots(const DevTiling& tl, const LaunchCfg&) {
   const int nbb = (tl.n_boundary + kBoundaryBlock - 1) / kBoundaryBlock;
   const int nvb = (tl.n_vert + 255) / 256;
-  const int a = tl.n_tiles + nbb;
+  const int a = tl.n_tiles + nbb;   // upper bound for every Op (persistent ones write fewer)
   return a > nvb ? a : nvb;
 }
 

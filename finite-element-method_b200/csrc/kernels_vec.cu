@@ -23,11 +23,23 @@ __device__ __forceinline__ bool counted(const RedMask& m, int i) {
   return m.bskip == nullptr || i < m.n_interior || m.bskip[i - m.n_interior] == 0;
 }
 
-// Sum red[0..n) in index order within each thread's strided slice, then a fixed tree.
+// Sum red[0..n): every thread sums a strided slice with 8 independent accumulators (8 loads in
+// flight: the single CTA is latency-bound), then a fixed tree.  The order depends only on n and
+// blockDim, never on timing: deterministic.
+constexpr int kFinalThreads = 1024;
 __device__ double final_sum(const double* red, int n) {
-  __shared__ double s[256];
-  double v = 0.0;
-  for (int i = threadIdx.x; i < n; i += blockDim.x) v += red[i];
+  __shared__ double s[kFinalThreads];
+  double a[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+  const int B = blockDim.x;
+  int i = threadIdx.x;
+  for (; i + 7 * B < n; i += 8 * B) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a[k] += red[i + k * B];
+  }
+#pragma unroll
+  for (int k = 0; k < 8; ++k)
+    if (i + k * B < n) a[k] += red[i + k * B];
+  const double v = ((a[0] + a[1]) + (a[2] + a[3])) + ((a[4] + a[5]) + (a[6] + a[7]));
   s[threadIdx.x] = v;
   __syncthreads();
   for (int o = blockDim.x / 2; o > 0; o >>= 1) {
@@ -63,7 +75,7 @@ __global__ void __launch_bounds__(256) k_cg_init(int n, ImplicitVecs iv, const f
 
 // kind 0: delta_new = sum (loop entry test) ; kind 1: alpha = delta_new / (d.q) ;
 // kind 2: delta_old = delta_new, delta_new = sum, beta, ++iters, loop test   (implicit.py:341,354,378-386)
-__global__ void __launch_bounds__(256) k_cg_scalar(int kind, int n_red, const double* red, SolveScalars* sc, float tol,
+__global__ void __launch_bounds__(kFinalThreads) k_cg_scalar(int kind, int n_red, const double* red, SolveScalars* sc, float tol,
                                                    int max_iter) {
   if (sc->done) return;
   const double s = final_sum(red, n_red);
@@ -119,7 +131,7 @@ __global__ void __launch_bounds__(256) k_cg_update_d(int n, ImplicitVecs iv, con
 }
 
 // Jacobi control flow, implicit.py:234-261, from err = ||b - A x|| of the CURRENT iterate.
-__global__ void __launch_bounds__(256) k_jacobi_decide(int n_red, const double* red, SolveScalars* sc, float tol,
+__global__ void __launch_bounds__(kFinalThreads) k_jacobi_decide(int n_red, const double* red, SolveScalars* sc, float tol,
                                                        int max_iter, int fixed) {
   if (sc->done) return;
   if (sc->terminal) {
@@ -214,7 +226,7 @@ __global__ void __launch_bounds__(256) k_fill(int n, float4* dst, float4 v) {
   if (i < n) dst[i] = v;
 }
 
-__global__ void __launch_bounds__(256) k_reduce_final(int n_red, const double* red, double* out) {
+__global__ void __launch_bounds__(kFinalThreads) k_reduce_final(int n_red, const double* red, double* out) {
   const double s = final_sum(red, n_red);
   if (threadIdx.x == 0) *out = s;
 }
@@ -282,11 +294,11 @@ void launch_cg_init(const LaunchCfg& c, int n_vert, ImplicitVecs iv, const float
   note_launch("cg_init", c.stream);
 }
 void launch_cg_delta0(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc, float tol, int max_iter) {
-  k_cg_scalar<<<1, 256, 0, c.stream>>>(0, n_red, red, sc, tol, max_iter);
+  k_cg_scalar<<<1, kFinalThreads, 0, c.stream>>>(0, n_red, red, sc, tol, max_iter);
   note_launch("cg_scalar0", c.stream);
 }
 void launch_cg_alpha(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc) {
-  k_cg_scalar<<<1, 256, 0, c.stream>>>(1, n_red, red, sc, 0.f, 0);
+  k_cg_scalar<<<1, kFinalThreads, 0, c.stream>>>(1, n_red, red, sc, 0.f, 0);
   note_launch("cg_alpha", c.stream);
 }
 void launch_cg_update_xr(const LaunchCfg& c, int n_vert, ImplicitVecs iv, double* red, SolveScalars* sc, RedMask mask) {
@@ -294,7 +306,7 @@ void launch_cg_update_xr(const LaunchCfg& c, int n_vert, ImplicitVecs iv, double
   note_launch("cg_update_xr", c.stream);
 }
 void launch_cg_beta(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc, float tol, int max_iter) {
-  k_cg_scalar<<<1, 256, 0, c.stream>>>(2, n_red, red, sc, tol, max_iter);
+  k_cg_scalar<<<1, kFinalThreads, 0, c.stream>>>(2, n_red, red, sc, tol, max_iter);
   note_launch("cg_beta", c.stream);
 }
 void launch_cg_update_d(const LaunchCfg& c, int n_vert, ImplicitVecs iv, const SolveScalars* sc) {
@@ -303,7 +315,7 @@ void launch_cg_update_d(const LaunchCfg& c, int n_vert, ImplicitVecs iv, const S
 }
 void launch_jacobi_decide(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc, float tol,
                           int max_iter, int fixed) {
-  k_jacobi_decide<<<1, 256, 0, c.stream>>>(n_red, red, sc, tol, max_iter, fixed);
+  k_jacobi_decide<<<1, kFinalThreads, 0, c.stream>>>(n_red, red, sc, tol, max_iter, fixed);
   note_launch("jacobi_decide", c.stream);
 }
 void launch_jacobi_update(const LaunchCfg& c, int n_vert, ImplicitVecs iv, SolveScalars* sc) {
@@ -323,7 +335,7 @@ void launch_fill(const LaunchCfg& c, int n, float4* dst, float4 v) {
   note_launch("fill", c.stream);
 }
 void launch_reduce_final(const LaunchCfg& c, int n_red, const double* red, double* out) {
-  k_reduce_final<<<1, 256, 0, c.stream>>>(n_red, red, out);
+  k_reduce_final<<<1, kFinalThreads, 0, c.stream>>>(n_red, red, out);
   note_launch("reduce_final", c.stream);
 }
 void launch_pack_vertex(const LaunchCfg& c, int, int n_vert, const int32_t* new_of_old, const float4* src, int comp0,

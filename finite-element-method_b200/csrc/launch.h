@@ -82,7 +82,9 @@ enum ApplyEpilogue { AP_PLAIN = 0, AP_DOT = 1, AP_RESID = 2 };
 void launch_apply(int dim, const LaunchCfg& c, const DevTiling& tl, Planes h, VertexState vs, float dt,
                   int transpose, const float4* in, float4* out, int epilogue, const float4* aux,
                   float4* resid_out, double* red, const SolveScalars* sc);
-int reduce_slots(const DevTiling& tl, const LaunchCfg& c);  // doubles needed in a reduction buffer
+int reduce_slots(const DevTiling& tl, const LaunchCfg& c);
+int apply_tile_grid(const DevTiling& tl);   // per-CTA reduction partials written by an operator pass
+int energy_tile_grid(const DevTiling& tl);  // ... by the energy pass  // doubles needed in a reduction buffer
 
 // CG / Jacobi vector kernels (all early-exit on sc->done)
 struct RedMask {           // which vertices this rank counts in global reductions (multi-GPU owner mask)

@@ -68,9 +68,29 @@ __device__ __forceinline__ void load_planes(const Planes& p, int slot, PlaneElem
 // Number of shared-memory staging planes of an Op: G_STAR ops stage the D x D contribution
 // matrix plus its negated column sum (the share of corner 0), so every incidence reads D
 // consecutive planes at a precomputed offset -- no branch on the corner in the gather.
+// (A float4-per-(corner, element) layout with one 16-byte load per incidence was measured 8 % SLOWER
+// on C4: random 16-byte shared loads cost >= 4 wavefronts each and the larger footprint shrinks the tiles.)
 template <int D, class Op>
 __host__ __device__ constexpr int n_planes() {
   return Op::GATHER == G_STAR ? Op::NSTAGE + D : Op::NSTAGE;
+}
+
+// stage one element's results plane-major (conflict-free stores)
+template <int D, class Op>
+__device__ __forceinline__ void stage_element(float* stage, int e, const float (&out)[Op::NSTAGE]) {
+  constexpr int S = kStride;
+  float* s = stage + e;
+#pragma unroll
+  for (int i = 0; i < Op::NSTAGE; ++i) s[i * S] = out[i];
+  if constexpr (Op::GATHER == G_STAR) {   // share of corner 0: f0 = -(sum of columns)   (explicit.py:42-49)
+#pragma unroll
+    for (int i = 0; i < D; ++i) {
+      float c = out[i];
+#pragma unroll
+      for (int j = 1; j < D; ++j) c += out[j * D + i];
+      s[(D * D + i) * S] = -c;
+    }
+  }
 }
 
 template <int D, int MODE, int NV>
@@ -117,13 +137,147 @@ __device__ __forceinline__ void gather_local_vertex(int n_rounds, const uint32_t
   }
 }
 
+// Persistent form: CTA c owns tiles c, c+G, c+2G, ...  While it works on tile t it already has, in flight or
+// landed, everything its next tile t' = t+G needs to start without a dependent global round trip:
+//   iteration start : TMA {descriptor, local-vertex table} of t' -> second buffer; TMA {JDS lists} of t;
+//                     L2 prefetch of the element planes / JDS / interior vertices of t'
+//   before the gather of t : vertex values of t' requested into registers (their table has landed)
+//   next iteration  : registers -> shared memory, first element loads already issued.
+template <int D, class Op>
+__global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile_persistent(DevTiling tl, typename Op::Args a) {
+  extern __shared__ float4 smem4[];
+  __shared__ float s_warp[32];
+  __shared__ uint64_t s_bar[3];          // [0],[1]: descriptor + local-vertex table buffers; [2]: JDS lists
+  __shared__ __align__(16) DevTile s_td[2];
+  if (Op::early_exit(a)) return;
+  int t = blockIdx.x;
+  if (t >= tl.n_tiles) return;
+  constexpr int S = kStride;
+  const TileSmem lay = tile_smem_layout(tl.max_lv, tl.max_rounds, tl.nc, n_planes<D, Op>());
+  char* smem = reinterpret_cast<char*>(smem4);
+  float4* sv = smem4;
+  auto lv_buf = [&](int i) { return reinterpret_cast<LocalVert*>(smem + (i ? lay.lvt2 : lay.lvt)); };
+  uint32_t* s_rounds = reinterpret_cast<uint32_t*>(smem + lay.rounds);
+  uint16_t* s_jds = reinterpret_cast<uint16_t*>(smem + lay.jds);
+  float* stage = reinterpret_cast<float*>(smem + lay.stage);
+  const int B = blockDim.x, G = gridDim.x, tid = threadIdx.x;
+
+  if (tid == 0) {
+    mbar_init(&s_bar[0], 1);
+    mbar_init(&s_bar[1], 1);
+    mbar_init(&s_bar[2], 1);
+    mbar_fence_init();
+    const DevTile d0 = tl.tiles[t];      // the only exposed descriptor fetch of this CTA
+    s_td[0] = d0;
+    const uint32_t lv_bytes = (uint32_t)round_up(d0.n_lv * 8, 16);
+    mbar_expect_tx(&s_bar[0], lv_bytes);
+    bulk_g2s(lv_buf(0), tl.lv + d0.lv_off, lv_bytes, &s_bar[0]);
+  }
+  __syncthreads();
+  mbar_wait(&s_bar[0], 0);
+  // vertex values of the tile about to be processed: two per thread in registers, the rest (tiles with
+  // more than 2*B local vertices: irregular meshes only) fetched directly at staging time
+  float4 vreg0 = make_float4(0.f, 0.f, 0.f, 0.f), vreg1 = vreg0;
+  {
+    const int n_lv = s_td[0].n_lv;
+    if (tid < n_lv) vreg0 = Op::load_vertex(a, lv_buf(0)[tid].gid);
+    if (tid + B < n_lv) vreg1 = Op::load_vertex(a, lv_buf(0)[tid + B].gid);
+  }
+
+  float red = 0.f;
+  for (int k = 0;; ++k) {
+    const int b = k & 1;
+    const DevTile& td = s_td[b];          // read on demand from shared memory (keeps registers for the math)
+    const LocalVert* s_lv = lv_buf(b);
+    const int n_elem = td.n_elem, slot_off = td.slot_off;
+    const int tn = t + G;
+    const bool has_next = tn < tl.n_tiles;
+    if (tid == 0) {
+      const uint32_t r_bytes = (uint32_t)round_up(td.n_rounds * 4, 16);
+      const uint32_t j_bytes = (uint32_t)round_up(td.n_elem * tl.nc * 2, 16);
+      mbar_expect_tx(&s_bar[2], r_bytes + j_bytes);
+      bulk_g2s(s_rounds, tl.rounds + td.rounds_off, r_bytes, &s_bar[2]);
+      bulk_g2s(s_jds, tl.jds + td.jds_off, j_bytes, &s_bar[2]);
+      if (has_next) {
+        const uint32_t lv_bytes = (uint32_t)round_up(td.nx_n_lv * 8, 16);
+        mbar_expect_tx(&s_bar[b ^ 1], lv_bytes + (uint32_t)sizeof(DevTile));
+        bulk_g2s(&s_td[b ^ 1], tl.tiles + tn, (uint32_t)sizeof(DevTile), &s_bar[b ^ 1]);
+        bulk_g2s(lv_buf(b ^ 1), tl.lv + td.nx_lv_off, lv_bytes, &s_bar[b ^ 1]);
+        Op::prefetch(a, td.nx_slot_off, (uint32_t)(round_up(td.nx_n_elem, 32) * 16));
+        bulk_prefetch_l2(tl.jds + td.nx_jds_off, (uint32_t)round_up(td.nx_n_elem * tl.nc * 2, 16));
+        if (td.nx_n_int > 0) Op::prefetch_verts(a, td.nx_int_base, (uint32_t)(td.nx_n_int * 16));
+      }
+    }
+    // element data of the first two elements of this thread: in flight while the vertices are staged
+    typename Op::Elem d0, d1;
+    if (tid < n_elem) Op::load(a, slot_off + tid, d0);
+    if (tid + B < n_elem) Op::load(a, slot_off + tid + B, d1);
+
+    if (tid < td.n_lv) sv[tid] = vreg0;
+    if (tid + B < td.n_lv) sv[tid + B] = vreg1;
+    for (int l = tid + 2 * B; l < td.n_lv; l += B) sv[l] = Op::load_vertex(a, s_lv[l].gid);
+    __syncthreads();
+
+    auto one = [&](int e, const typename Op::Elem& d) {
+      float out[Op::NSTAGE];
+      Op::compute(a, slot_off + e, d, sv, out, red);
+      stage_element<D, Op>(stage, e, out);
+    };
+    for (int e = tid; e < n_elem; e += 2 * B) {
+      const bool two = e + B < n_elem;
+      if (e != tid) {
+        Op::load(a, slot_off + e, d0);
+        if (two) Op::load(a, slot_off + e + B, d1);
+      }
+      one(e, d0);
+      if (two) one(e + B, d1);
+    }
+    __syncthreads();
+
+    // the next tile's vertex values: its local-vertex table landed during the element phase
+    if (has_next) {
+      mbar_wait(&s_bar[b ^ 1], (uint32_t)(((k + 1) >> 1) & 1));
+      const int n_lv = s_td[b ^ 1].n_lv;
+      const LocalVert* nlv = lv_buf(b ^ 1);
+      if (tid < n_lv) vreg0 = Op::load_vertex(a, nlv[tid].gid);
+      if (tid + B < n_lv) vreg1 = Op::load_vertex(a, nlv[tid + B].gid);
+    }
+    mbar_wait(&s_bar[2], (uint32_t)(k & 1));
+
+    for (int l = tid; l < td.n_lv; l += B) {
+      const LocalVert v = s_lv[l];
+      // per-vertex global operand of the epilogue (e.g. vel): requested before the gather hides its latency
+      float4 pre = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (v.part < 0) pre = Op::pre(a, v.gid);
+      float acc[D];
+      gather_local_vertex<D, Op::GATHER, (Op::NSTAGE < D ? Op::NSTAGE : D)>(td.n_rounds, s_rounds, s_jds, stage, l,
+                                                                           Op::w0(), acc);
+      if (v.part < 0) {
+        Op::vertex(a, v.gid, sv[l], pre, acc, red);
+      } else {
+        float4 p;
+        p.x = acc[0]; p.y = acc[1]; p.z = D == 3 ? acc[D - 1] : 0.f; p.w = 0.f;
+        Op::partial_buf(a)[v.part] = p;
+      }
+    }
+    if (!has_next) break;
+    t = tn;
+    __syncthreads();   // staging planes, vertex values and JDS lists are free for the next tile
+  }
+  if (Op::REDUCE) {
+    const float r = block_sum(red, s_warp);
+    if (tid == 0) Op::red_buf(a)[blockIdx.x] = (double)r;
+  }
+}
+
+// One CTA per tile.
 template <int D, class Op>
 __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile(DevTiling tl, typename Op::Args a) {
   extern __shared__ float4 smem4[];
   __shared__ float s_warp[32];
   __shared__ uint64_t s_bar[2];   // [0]: local-vertex table landed, [1]: JDS lists landed
   if (Op::early_exit(a)) return;
-  const TileDesc td = tl.tiles[blockIdx.x];
+  const DevTile td = tl.tiles[blockIdx.x];
   constexpr int S = kStride;
   const TileSmem lay = tile_smem_layout(tl.max_lv, tl.max_rounds, tl.nc, n_planes<D, Op>());
   char* smem = reinterpret_cast<char*>(smem4);
@@ -148,7 +302,7 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile(DevTiling tl, 
     // L2 prefetch of the tile that will occupy this SM slot after us
     const int nxt = blockIdx.x + tl.prefetch_dist;
     if (tl.prefetch_dist > 0 && nxt < tl.n_tiles) {
-      const TileDesc tn = tl.tiles[nxt];
+      const DevTile tn = tl.tiles[nxt];
       Op::prefetch(a, tn.slot_off, (uint32_t)(round_up(tn.n_elem, 32) * 16));
       bulk_prefetch_l2(tl.lv + tn.lv_off, (uint32_t)round_up(tn.n_lv * 8, 16));
       bulk_prefetch_l2(tl.jds + tn.jds_off, (uint32_t)round_up(tn.n_elem * tl.nc * 2, 16));
@@ -171,18 +325,7 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile(DevTiling tl, 
   auto one = [&](int e, const typename Op::Elem& d) {
     float out[Op::NSTAGE];
     Op::compute(a, td.slot_off + e, d, sv, out, red);
-    float* s = stage + e;
-#pragma unroll
-    for (int k = 0; k < Op::NSTAGE; ++k) s[k * S] = out[k];
-    if (Op::GATHER == G_STAR) {   // share of corner 0: f0 = -(sum of columns)   (explicit.py:42-49)
-#pragma unroll
-      for (int i = 0; i < D; ++i) {
-        float t = out[i];
-#pragma unroll
-        for (int j = 1; j < D; ++j) t += out[j * D + i];
-        s[(D * D + i) * S] = -t;
-      }
-    }
+    stage_element<D, Op>(stage, e, out);
   };
   for (int e = threadIdx.x; e < td.n_elem; e += 2 * B) {
     const bool two = e + B < td.n_elem;
@@ -217,7 +360,6 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile(DevTiling tl, 
     if (threadIdx.x == 0) Op::red_buf(a)[blockIdx.x] = (double)r;
   }
 }
-
 constexpr int kBoundaryBlock = 256;
 
 template <int D, class Op>
@@ -229,17 +371,28 @@ __global__ void __launch_bounds__(kBoundaryBlock) k_boundary(DevTiling tl, typen
   if (b < tl.n_boundary) {
     const float4* part = Op::partial_buf(a);
     const int s0 = tl.bptr[b], s1 = tl.bptr[b + 1];
+    const int gid = tl.n_interior + b;
+    // the vertex operands do not depend on the partial sums: request them first
+    const float4 vtx = Op::load_vertex(a, gid);
+    const float4 pre = Op::pre(a, gid);
     float acc[D];
 #pragma unroll
     for (int i = 0; i < D; ++i) acc[i] = 0.f;
-    for (int s = s0; s < s1; ++s) {
-      const float4 p = part[s];
-      acc[0] += p.x;
-      acc[1] += p.y;
-      if (D == 3) acc[D - 1] += p.z;
+    // four slots per trip: independent loads, adds in slot order (same sums as one at a time)
+    for (int s = s0; s < s1; s += 4) {
+      float4 p[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) p[k] = s + k < s1 ? __ldcs(part + s + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        if (s + k < s1) {
+          acc[0] += p[k].x;
+          acc[1] += p[k].y;
+          if (D == 3) acc[D - 1] += p[k].z;
+        }
+      }
     }
-    const int gid = tl.n_interior + b;
-    Op::vertex(a, gid, Op::load_vertex(a, gid), Op::pre(a, gid), acc, red);
+    Op::vertex(a, gid, vtx, pre, acc, red);
     if (Op::REDUCE && tl.bskip && tl.bskip[b]) red = 0.f;   // shared vertex owned by the neighbouring rank
   }
   if (Op::REDUCE) {
@@ -255,12 +408,17 @@ __device__ __forceinline__ void prefetch_planes(const Planes& p, int slot, uint3
   if (three) bulk_prefetch_l2(p.p2 + slot, bytes);
 }
 
+// CTAs of the tile kernel of an Op == number of per-CTA reduction partials it writes
+template <class Op>
+inline int tile_grid(const DevTiling& tl) { return Op::PERSIST ? tl.grid : tl.n_tiles; }
+
 template <int D, class Op>
 inline void run_tile_pass(const char* name, const LaunchCfg& c, const DevTiling& tl, const typename Op::Args& a) {
   static int attr_set[64] = {};  // per device (the attribute lives in the device's context): bytes allowed so far
   const int smem = tile_smem_layout(tl.max_lv, tl.max_rounds, tl.nc, n_planes<D, Op>()).total;
+  auto* kern = Op::PERSIST ? k_tile_persistent<D, Op> : k_tile<D, Op>;
   if (smem > attr_set[c.device & 63]) {
-    const cudaError_t e = cudaFuncSetAttribute(k_tile<D, Op>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    const cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) {
       cudaGetLastError();
       throw std::runtime_error(std::string(name) + ": cannot reserve shared memory: " + cudaGetErrorString(e));
@@ -268,13 +426,13 @@ inline void run_tile_pass(const char* name, const LaunchCfg& c, const DevTiling&
     attr_set[c.device & 63] = smem;
   }
   if (c.phase != 2) {
-    k_tile<D, Op><<<tl.n_tiles, Op::BLOCK, smem, c.stream>>>(tl, a);
+    kern<<<tile_grid<Op>(tl), Op::BLOCK, smem, c.stream>>>(tl, a);
     note_launch(name, c.stream);
   }
   if (c.ev_mid) cudaEventRecord(c.ev_mid, c.stream);
   if (tl.n_boundary > 0 && c.phase != 1) {
     const int nb = (tl.n_boundary + kBoundaryBlock - 1) / kBoundaryBlock;
-    k_boundary<D, Op><<<nb, kBoundaryBlock, 0, c.stream>>>(tl, a, tl.n_tiles);
+    k_boundary<D, Op><<<nb, kBoundaryBlock, 0, c.stream>>>(tl, a, tile_grid<Op>(tl));
     note_launch(name, c.stream);
   }
 }

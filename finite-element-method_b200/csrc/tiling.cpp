@@ -278,6 +278,33 @@ std::string build_tiling(int dim, int n_vert, int n_elem, const float* verts,
         const int l = li[(size_t)i * nc + c];
         inc[fill[l]++] = (uint16_t)jds_entry(dim, i, c);
       }
+    // Bank-aware order of every vertex's list.  In round k the lanes of a warp (32 consecutive local
+    // vertices) read staging word (plane * kStride + slot) of their k-th incidence: bank = slot % 32 for
+    // every plane.  Pick, round by round, for each lane an unused incidence whose bank is the least
+    // occupied in this round -- most rounds become conflict-free (random order: ~3.5 wavefronts per load).
+    // Only the (fixed) summation order changes.
+    static_assert(kStride % 32 == 0, "staging planes must start on bank 0");
+#ifndef FEMB_NO_BANK_ORDER
+    for (int w0 = 0; w0 < nl; w0 += 32) {
+      const int w1 = std::min(nl, w0 + 32);
+      const int vmax = tval[ti][w0];                // sorted descending: the group's largest valence
+      for (int k = 0; k < vmax; ++k) {
+        int occ[32] = {0};
+        for (int l = w1 - 1; l >= w0; --l) {         // fewest remaining choices first
+          const int val = tval[ti][l];
+          if (val <= k) continue;
+          uint16_t* lst = inc.data() + start[l];
+          int best = k, best_occ = occ[lst[k] & 31];
+          for (int j = k + 1; j < val && best_occ > 0; ++j) {
+            const int oc = occ[lst[j] & 31];
+            if (oc < best_occ) { best = j; best_occ = oc; }
+          }
+          std::swap(lst[k], lst[best]);
+          occ[lst[k] & 31]++;
+        }
+      }
+    }
+#endif
     // jagged-diagonal layout: round k holds entry k of every vertex with valence > k
     int64_t off = d.jds_off;
     for (int k = 0; k < d.n_rounds; ++k) {
