@@ -165,7 +165,7 @@ def run_ours(args):
     torch.cuda.set_stream(stream)
     h.set_stream(stream.cuda_stream)
     if halo is not None:
-        halo.attach(h)
+        halo.attach(h, mode=args.comm)
     info = h.info()
     vel0 = np.zeros_like(pos0)
     h.set(c.F_POS, pos0)
@@ -274,7 +274,9 @@ def run_ours(args):
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic Kuhn tet box, seeded 10% h vertex jitter, random-free material from config/demo_3d.json",
             "config": {"workload": args.workload, "cells": list(w["cells"]), "n_tets": ne_global, "n_verts": nv_global,
-                       "dt": dt, "partition": "x-slabs, %d rank(s)" % world, "tile_elems": info["tile_elems"],
+                       "dt": dt, "partition": "x-slabs, %d rank(s)" % world,
+                       "comm": None if halo is None else ("peer memory (in-kernel NVLink stores + flags)" if halo.peer
+                                                          else "NCCL P2P + all_reduce"), "tile_elems": info["tile_elems"],
                        "n_tiles_rank0": info["n_tiles"], "cache": "inputs %.0f MB per rank > 126 MB L2" %
                        (algorithmic_bytes(kind, len(tets), len(verts)) / 1e6),
                        "state_reset_every": RESET_EVERY if kind == "explicit" else None, "state_finite": finite,
@@ -442,6 +444,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=20)
     ap.add_argument("--cpu-cells", type=int, nargs=3, default=[96, 96, 96], help="CPU sample size in cells")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--comm", default=None, choices=["peer", "nccl"], help="multi-GPU transport (default: peer memory)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

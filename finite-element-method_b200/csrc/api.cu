@@ -84,10 +84,13 @@ int femb_object_create(const femb_desc* d, femb_object** out) {
       for (int k = 0; k < dim; ++k) pos[(size_t)v * dim + k] = d->verts[(size_t)v * dim + k] + d->center[k];
 
     int T = d->tile_elems > 0 ? std::min(d->tile_elems, kStride) : kStride;
+    cudaDeviceProp prop{};
+    FEMB_CUDA(cudaGetDeviceProperties(&prop, o->device));
+    const int wave = prop.multiProcessorCount * kMinCtas;   // tile CTAs resident at once
     for (;;) {
       if (d->n_halo < 0 || (d->n_halo > 0 && !d->halo_verts)) throw ArgError("bad halo vertex list");
       const std::string err = build_tiling(dim, d->n_vert, d->n_elem, pos.data(), d->elems, T, o->til, d->n_halo,
-                                           d->halo_verts);
+                                           d->halo_verts, wave);
       if (!err.empty()) throw ArgError(err);
       if (tile_smem_bytes(o->til) <= kMaxSmem) break;
       if (T <= 64) throw LimitError("tiling does not fit shared memory even with 64-element tiles");
@@ -97,8 +100,6 @@ int femb_object_create(const femb_desc* d, femb_object** out) {
 
     FEMB_CUDA(cudaStreamCreateWithFlags(&o->stream, cudaStreamNonBlocking));
     o->own_stream = true;
-    cudaDeviceProp prop{};
-    FEMB_CUDA(cudaGetDeviceProperties(&prop, o->device));
     o->cfg = LaunchCfg{o->stream, 256, tile_smem_bytes(t), prop.multiProcessorCount, o->device};
 
     auto upload = [&](auto*& dst, const auto& vec) {
@@ -193,6 +194,7 @@ int femb_object_destroy(femb_object* o) {
   cudaSetDevice(o->device);
   if (o->stream) cudaStreamSynchronize(o->stream);
   if (o->graph.exec) cudaGraphExecDestroy(o->graph.exec);
+  if (o->solve_graph.exec) cudaGraphExecDestroy(o->solve_graph.exec);
   for (void* p : o->allocs) cudaFree(p);
   if (o->h_sc) cudaFreeHost(o->h_sc);
   if (o->own_stream && o->stream) cudaStreamDestroy(o->stream);
@@ -228,6 +230,7 @@ int femb_set_stream(femb_object* o, void* s) {
   o->stream = static_cast<cudaStream_t>(s);
   o->cfg.stream = o->stream;
   if (o->graph.exec) { cudaGraphExecDestroy(o->graph.exec); o->graph = StepGraph(); }
+  if (o->solve_graph.exec) { cudaGraphExecDestroy(o->solve_graph.exec); o->solve_graph = SolveGraph(); }
   FEMB_CATCH
 }
 
@@ -295,9 +298,23 @@ int femb_explicit_step(femb_object* o, float dt, const float* g_dir, int32_t n_s
   FEMB_CUDA(cudaSetDevice(o->device));
   const KinArgs kin = o->kin_args(dt, g_dir);
   o->prep_full_pass();
+  if (o->halo.n > 0 && !o->peer_on)
+    throw StateError("object has halo vertices: bind peers (femb_peer_bind) or drive femb_explicit_step_phase");
   auto run = [&]() {
-    for (int s = 0; s < n_steps; ++s)
-      launch_explicit(o->dim, EX_STEP, o->cfg, o->dtl, o->e, o->vs, o->mat, kin, nullptr, nullptr);
+    for (int s = 0; s < n_steps; ++s) {
+      if (!o->peer_on) {
+        launch_explicit(o->dim, EX_STEP, o->cfg, o->dtl, o->e, o->vs, o->mat, kin, nullptr, nullptr);
+        continue;
+      }
+      // slab rank: tile kernel | shared-vertex sums straight into the neighbours' memory | boundary kernel
+      LaunchCfg c1 = o->cfg, c2 = o->cfg;
+      c1.phase = 1; c2.phase = 2;
+      launch_explicit(o->dim, EX_STEP, c1, o->dtl, o->e, o->vs, o->mat, kin, nullptr, nullptr);
+      launch_halo_send(c1, o->dtl, o->peer, o->halo, o->vs.partial, o->vs.pos, 0);
+      launch_halo_recv(c2, o->dtl, o->peer, o->halo, o->vs.partial, o->vs.pos, 0);
+      o->halo_dirty = true;
+      launch_explicit(o->dim, EX_STEP, c2, o->dtl, o->e, o->vs, o->mat, kin, nullptr, nullptr);
+    }
   };
   // (the legacy default stream cannot be captured)
   if (n_steps < 4 || o->stream == nullptr || o->stream == cudaStreamLegacy) {
@@ -372,6 +389,60 @@ int femb_halo_bind(femb_object* o, void* send_dev, void* recv_dev) {
   FEMB_CATCH
 }
 
+int femb_comm_bytes(int32_t max_halo, size_t* bytes_out, int32_t* recv_stride_out) {
+  FEMB_TRY
+  if (max_halo <= 0 || !bytes_out || !recv_stride_out) throw ArgError("femb_comm_bytes: bad argument");
+  size_t a, b, stride;
+  *bytes_out = comm_layout(max_halo, &a, &b, &stride);
+  *recv_stride_out = (int32_t)stride;
+  FEMB_CATCH
+}
+
+int femb_peer_bind(femb_object* o, const femb_peer_desc* d) {
+  FEMB_TRY
+  if (!o || !d || !d->bufs) throw ArgError("femb_peer_bind: NULL argument");
+  if (o->halo.n == 0) throw StateError("object was created without halo vertices");
+  if (d->world < 2 || d->world > kMaxRanks || d->rank < 0 || d->rank >= d->world) throw ArgError("bad rank / world size");
+  if (d->n_left < 0 || d->n_left > o->halo.n) throw ArgError("bad n_left");
+  if ((d->n_left > 0) != (d->left >= 0) || (d->n_left < o->halo.n) != (d->right >= 0))
+    throw ArgError("neighbour ranks do not match the halo split");
+  FEMB_CUDA(cudaSetDevice(o->device));
+  PeerComm pc{};
+  for (int r = 0; r < d->world; ++r) {
+    if (!d->bufs[r]) throw ArgError("NULL comm buffer");
+    pc.all[r] = static_cast<char*>(d->bufs[r]);
+  }
+  pc.self = pc.all[d->rank];
+  pc.left = d->left >= 0 ? pc.all[d->left] : nullptr;
+  pc.right = d->right >= 0 ? pc.all[d->right] : nullptr;
+  pc.rank = d->rank; pc.world = d->world; pc.n_left = d->n_left;
+  pc.left_dst_off = d->left_dst_off; pc.right_dst_off = d->right_dst_off;
+  comm_layout(o->halo.n, &pc.recv_off, &pc.slot_off, &pc.recv_stride);
+  if (d->recv_stride < o->halo.n) throw ArgError("recv_stride must be the value femb_comm_bytes returned for the largest halo");
+  pc.recv_stride = (size_t)d->recv_stride;   // common to all ranks: remote addresses are computed with it
+  pc.st = o->alloc<CommState>(1);
+  o->d_allred_own = o->alloc<double>(1);
+  o->d_allred = o->d_allred_own;
+  FEMB_CUDA(cudaStreamSynchronize(o->stream));
+  o->peer = pc;
+  o->peer_on = true;
+  if (o->graph.exec) { cudaGraphExecDestroy(o->graph.exec); o->graph = StepGraph(); }
+  if (o->solve_graph.exec) { cudaGraphExecDestroy(o->solve_graph.exec); o->solve_graph = SolveGraph(); }
+  FEMB_CATCH
+}
+
+// completes the lumped masses of shared vertices through the peer buffers (once, after femb_peer_bind)
+int femb_peer_mass(femb_object* o) {
+  FEMB_TRY
+  if (!o || !o->peer_on) throw StateError("femb_peer_mass: peers are not bound");
+  FEMB_CUDA(cudaSetDevice(o->device));
+  launch_halo_send(o->cfg, o->dtl, o->peer, o->halo, nullptr, o->vs.pos, 1);
+  launch_halo_recv(o->cfg, o->dtl, o->peer, o->halo, nullptr, o->vs.pos, 1);
+  FEMB_CUDA(cudaStreamSynchronize(o->stream));
+  o->check_comm_error();
+  FEMB_CATCH
+}
+
 static void need_halo(const femb_object* o, int phase) {
   if (!o) throw ArgError("NULL object");
   if (phase != 1 && phase != 2) throw ArgError("phase must be 1 or 2");
@@ -414,6 +485,7 @@ int femb_sync(femb_object* o) {
   FEMB_TRY
   if (!o) throw ArgError("NULL object");
   FEMB_CUDA(cudaStreamSynchronize(o->stream));
+  o->check_comm_error();
   FEMB_CATCH
 }
 

@@ -31,6 +31,7 @@ static int apply_red_slots(const femb_object* o) { return apply_tile_grid(o->dtl
 static void poll(femb_object* o) {
   FEMB_CUDA(cudaMemcpyAsync(o->h_sc, o->d_sc, sizeof(SolveScalars), cudaMemcpyDeviceToHost, o->stream));
   FEMB_CUDA(cudaStreamSynchronize(o->stream));
+  o->check_comm_error();
 }
 
 static void assemble(femb_object* o, float dt, bool with_diag) {
@@ -61,6 +62,18 @@ struct Builder {
       add([ob, f] { ob->prep_full_pass(); f(ob->cfg); });
       return;
     }
+    if (ob->peer_on) {   // halo sums through peer memory, inside our own kernels: no communication point
+      add([ob, f] {
+        LaunchCfg c1 = ob->cfg, c2 = ob->cfg;
+        c1.phase = 1; c2.phase = 2;
+        f(c1);
+        launch_halo_send(c1, ob->dtl, ob->peer, ob->halo, ob->vs.partial, ob->vs.pos, 0);
+        launch_halo_recv(c2, ob->dtl, ob->peer, ob->halo, ob->vs.partial, ob->vs.pos, 0);
+        ob->halo_dirty = true;
+        f(c2);
+      });
+      return;
+    }
     add([ob, f] {
       LaunchCfg c = ob->cfg;
       c.phase = 1;
@@ -84,6 +97,14 @@ struct Builder {
       add([ob, n_red, consume] { consume(n_red, ob->d_red); });
       return;
     }
+    if (ob->peer_on) {
+      add([ob, n_red, consume] {
+        launch_reduce_final(ob->cfg, n_red, ob->d_red, ob->d_allred);
+        launch_allsum(ob->cfg, ob->peer, ob->d_allred);
+        consume(1, ob->d_allred);
+      });
+      return;
+    }
     add([ob, n_red] { launch_reduce_final(ob->cfg, n_red, ob->d_red, ob->d_allred); }, FEMB_COMM_ALLREDUCE);
     add([ob, consume] { consume(1, ob->d_allred); });
   }
@@ -91,7 +112,7 @@ struct Builder {
 
 void build_program(femb_object* o, SolveProgram& P, float dt, int method, int preconditioned, int max_iter, float tol) {
   const bool dist = o->halo.n > 0;
-  if (dist && (!o->halo.send || !o->halo.recv || !o->d_allred))
+  if (dist && !o->peer_on && (!o->halo.send || !o->halo.recv || !o->d_allred))
     throw StateError("multi-GPU solve: bind the halo buffers (femb_halo_bind) and the allreduce buffer (femb_reduce_bind) first");
   P.fixed = (tol == 0.f);                              // benchmark mode: exactly max_iter iterations
   if (tol < 0.f) tol = 1e-5f;                          // implicit.py:236,341
@@ -220,8 +241,8 @@ int femb_implicit_solve(femb_object* o, float dt, int32_t method, int32_t precon
                         float tol, int32_t* iters_out, float* resid_out) {
   FEMB_TRY
   check_solve_args(o, method);
-  if (o->halo.n > 0)
-    throw StateError("object has halo vertices: drive the solve with femb_implicit_solve_begin/_advance/_finish");
+  if (o->halo.n > 0 && !o->peer_on)
+    throw StateError("object has halo vertices: bind peers, or drive the solve with femb_implicit_solve_begin/_advance/_finish");
   FEMB_CUDA(cudaSetDevice(o->device));
   o->prog.reset(new SolveProgram());
   SolveProgram& P = *o->prog;
@@ -229,10 +250,42 @@ int femb_implicit_solve(femb_object* o, float dt, int32_t method, int32_t precon
   advance(o);                                          // prologue (no communication on one GPU)
   // Jacobi needs one more residual evaluation than updates, plus the pass that sets `done`
   const int n_it = method == 1 ? P.max_iter : P.max_iter + 2;
+  // one iteration (all its kernels, peer-memory communication included) as a CUDA graph: the argument
+  // values of an iteration never change, so the graph is cached per (dt, method, tolerance ...)
+  SolveGraph& g = o->solve_graph;
+  const bool use_graph = n_it >= 4 && o->stream != nullptr && o->stream != cudaStreamLegacy;
+  if (use_graph) {
+    const bool hit = g.exec && g.dt == dt && g.tol == tol && g.method == method && g.pre == preconditioned &&
+                     g.max_iter == P.max_iter;
+    if (!hit) {
+      if (g.exec) { cudaGraphExecDestroy(g.exec); g = SolveGraph(); }
+      cudaGraph_t graph = nullptr;
+      const uint64_t before = launch_count();
+      FEMB_CUDA(cudaStreamBeginCapture(o->stream, cudaStreamCaptureModeThreadLocal));
+      try {
+        advance(o);
+      } catch (...) {
+        cudaStreamEndCapture(o->stream, &graph);
+        if (graph) cudaGraphDestroy(graph);
+        throw;
+      }
+      FEMB_CUDA(cudaStreamEndCapture(o->stream, &graph));
+      const cudaError_t ie = cudaGraphInstantiate(&g.exec, graph, 0);
+      cudaGraphDestroy(graph);
+      cuda_check(ie, "cudaGraphInstantiate");
+      g.launches = launch_count() - before;
+      g.dt = dt; g.tol = tol; g.method = method; g.pre = preconditioned; g.max_iter = P.max_iter;
+    }
+  }
   int chunk = 4, since_poll = 0;
   bool finished = false;
   for (int it = 0; it < n_it && !finished; ++it) {
-    advance(o);
+    if (use_graph) {
+      FEMB_CUDA(cudaGraphLaunch(g.exec, o->stream));
+      for (uint64_t i = 0; i < g.launches; ++i) note_launch("graph", o->stream);
+    } else {
+      advance(o);
+    }
     if (!P.fixed && ++since_poll >= chunk) {
       poll(o);
       finished = (o->h_sc->done | o->h_sc->terminal) != 0;

@@ -57,6 +57,36 @@ struct Halo {                    // vertices shared with a neighbouring rank (sl
   float4* send = nullptr;        // [n] caller-owned device buffers (torch tensors / peer memory)
   float4* recv = nullptr;
 };
+// ---- peer-memory communication (kernels_comm.cu): the comm buffer every rank exposes to all ranks
+constexpr int kMaxRanks = 16;
+struct CommHeader {              // at offset 0 of a comm buffer; written by REMOTE ranks
+  uint32_t halo_flag[2];         // [0]: sequence released by the LEFT neighbour, [1]: by the RIGHT one
+  uint32_t ar_flag[kMaxRanks];   // [r]: dot-product sequence released by rank r
+  uint32_t pad[46];              // header = 256 bytes
+};
+struct CommState {               // LOCAL device memory: sequence counters (graph-replayable) and the error flag
+  uint32_t send_seq, recv_seq, ar_seq, pack_count, unpack_count, error, pad0, pad1;
+};
+struct PeerComm {                // kernel argument
+  char* self;                    // my comm buffer
+  char* left;                    // neighbours' comm buffers (peer-mapped), nullptr at the ends of the slab chain
+  char* right;
+  char* all[kMaxRanks];          // every rank's comm buffer, all[rank] == self
+  int rank, world;
+  int n_left;                    // halo entries [0, n_left) go to / come from the left neighbour
+  int left_dst_off, right_dst_off;   // where my planes start in the neighbours' receive arrays
+  size_t recv_off, slot_off, recv_stride;
+  CommState* st;
+};
+size_t comm_layout(int n_halo, size_t* recv_off, size_t* slot_off, size_t* recv_stride);
+// what: 0 partial sums, 1 lumped masses
+void launch_halo_send(const LaunchCfg& c, const DevTiling& tl, const PeerComm& pc, Halo h, const float4* partial,
+                      const float4* pos, int what);
+void launch_halo_recv(const LaunchCfg& c, const DevTiling& tl, const PeerComm& pc, Halo h, float4* partial,
+                      float4* pos, int what);
+// *value = sum over ranks of *value, identical bits on every rank
+void launch_allsum(const LaunchCfg& c, const PeerComm& pc, double* value);
+
 // send[k] = sum of the local partial slots of halo vertex k ; partial[remote slot of k] = recv[k]
 void launch_halo_pack(const LaunchCfg& c, const DevTiling& tl, Halo h, const float4* partial);
 void launch_halo_unpack(const LaunchCfg& c, const DevTiling& tl, Halo h, float4* partial);

@@ -32,6 +32,13 @@ inline void cuda_check(cudaError_t e, const char* what) {
 }
 #define FEMB_CUDA(x) ::femb::cuda_check((x), #x)
 
+struct SolveGraph {         // cached CUDA graph of ONE solver iteration
+  cudaGraphExec_t exec = nullptr;
+  float dt = 0.f, tol = 0.f;
+  int method = -1, pre = -1, max_iter = 0;
+  uint64_t launches = 0;
+};
+
 struct StepGraph {          // cached CUDA graph of n fused explicit steps
   cudaGraphExec_t exec = nullptr;
   float dt = 0.f, g[3] = {0, 0, 0}, damp = 0.f;
@@ -84,9 +91,13 @@ struct femb_object {
   bool own_stream = false;
   femb::LaunchCfg cfg{};
   femb::StepGraph graph;
+  femb::SolveGraph solve_graph;
   std::unique_ptr<femb::SolveProgram> prog;   // implicit solve in progress (begin/advance/finish)
   int last_method = 1;              // method of the most recent solve (what `resid` means)
   double* d_allred = nullptr;       // multi-GPU: caller-owned device doubles the caller sum-allreduces
+  femb::PeerComm peer{};            // multi-GPU over peer memory (femb_peer_bind); peer_on: no caller-side collectives
+  bool peer_on = false;
+  double* d_allred_own = nullptr;   // library-owned scalar for the in-kernel all-sum
   femb::Halo halo;                  // multi-GPU: vertices shared with neighbouring ranks
   bool halo_dirty = false;          // remote partial slots hold data of an earlier exchange
   // every un-phased pass on a halo object must see zeros in the remote slots
@@ -108,6 +119,13 @@ struct femb_object {
     device_bytes += (int64_t)bytes;
     if (zero) FEMB_CUDA(cudaMemsetAsync(p, 0, bytes, stream));
     return static_cast<T*>(p);
+  }
+  // a peer wait that timed out leaves CommState.error set: surface it (call after a stream sync)
+  void check_comm_error() {
+    if (!peer_on) return;
+    uint32_t err = 0;
+    FEMB_CUDA(cudaMemcpy(&err, &peer.st->error, sizeof(err), cudaMemcpyDeviceToHost));
+    if (err) throw femb::CudaError("multi-GPU: timed out waiting for a peer rank (halo flag / dot-product slot)");
   }
   void ensure_stage(size_t floats);
   femb::KinArgs kin_args(float dt, const float* g_dir) const;

@@ -30,6 +30,24 @@ enum GatherMode {
   G_UNIFORM = 1   // every corner gets the staged vector, corner 0 weighted by Op::w0()
 };
 
+#ifndef FEMB_PDL
+#define FEMB_PDL 0
+#endif
+// Programmatic dependent launch (off by default: measured no gain on C4 -- the register file is full of
+// tile CTAs until the very tail): the tile kernels let the boundary kernel that follows them be scheduled
+// as soon as every tile CTA has started; the boundary kernel waits (grid_dependency_wait) for their
+// completion before it touches the partial sums.
+__device__ __forceinline__ void grid_launch_dependents() {
+#if FEMB_PDL
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+#endif
+}
+__device__ __forceinline__ void grid_dependency_wait() {
+#if FEMB_PDL
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+#endif
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -149,6 +167,7 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile_persistent(Dev
   __shared__ float s_warp[32];
   __shared__ uint64_t s_bar[3];          // [0],[1]: descriptor + local-vertex table buffers; [2]: JDS lists
   __shared__ __align__(16) DevTile s_td[2];
+  grid_launch_dependents();
   if (Op::early_exit(a)) return;
   int t = blockIdx.x;
   if (t >= tl.n_tiles) return;
@@ -276,6 +295,7 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile(DevTiling tl, 
   extern __shared__ float4 smem4[];
   __shared__ float s_warp[32];
   __shared__ uint64_t s_bar[2];   // [0]: local-vertex table landed, [1]: JDS lists landed
+  grid_launch_dependents();
   if (Op::early_exit(a)) return;
   const DevTile td = tl.tiles[blockIdx.x];
   constexpr int S = kStride;
@@ -375,6 +395,9 @@ __global__ void __launch_bounds__(kBoundaryBlock) k_boundary(DevTiling tl, typen
     // the vertex operands do not depend on the partial sums: request them first
     const float4 vtx = Op::load_vertex(a, gid);
     const float4 pre = Op::pre(a, gid);
+    // Launched with programmatic stream serialization: everything above overlaps the tail of the tile
+    // kernel; the partial sums it wrote are visible only after this wait (no-op in a plain launch).
+    grid_dependency_wait();
     float acc[D];
 #pragma unroll
     for (int i = 0; i < D; ++i) acc[i] = 0.f;
@@ -432,7 +455,22 @@ inline void run_tile_pass(const char* name, const LaunchCfg& c, const DevTiling&
   if (c.ev_mid) cudaEventRecord(c.ev_mid, c.stream);
   if (tl.n_boundary > 0 && c.phase != 1) {
     const int nb = (tl.n_boundary + kBoundaryBlock - 1) / kBoundaryBlock;
+#if FEMB_PDL
+    // programmatic dependent launch: the boundary kernel's CTAs are scheduled while the tile kernel drains
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = dim3((unsigned)nb);
+    lc.blockDim = dim3(kBoundaryBlock);
+    lc.dynamicSmemBytes = 0;
+    lc.stream = c.stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    lc.attrs = at;
+    lc.numAttrs = 1;
+    cudaLaunchKernelEx(&lc, k_boundary<D, Op>, tl, a, tile_grid<Op>(tl));
+#else
     k_boundary<D, Op><<<nb, kBoundaryBlock, 0, c.stream>>>(tl, a, tile_grid<Op>(tl));
+#endif
     note_launch(name, c.stream);
   }
 }

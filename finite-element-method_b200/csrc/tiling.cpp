@@ -17,13 +17,11 @@ struct Rcb {
   int32_t* idx;
   std::vector<char>* is_start;
 
-  void run(int lo, int hi) {
+  // elements [lo, hi) become exactly k tiles of (nearly) equal size
+  void run(int lo, int hi, int k) {
     const int n = hi - lo;
     (*is_start)[lo] = 1;
-    if (n <= T) return;
-    // aim for ~88% fill so that cuts can snap to coordinate gaps (planar tile faces)
-    const int Tf = T - T / 8;
-    const int k = std::max(2, (n + Tf - 1) / Tf);
+    if (k <= 1) return;
     const int kl = k / 2;
     int m = lo + (int)((int64_t)n * kl / k);
     // longest axis of the centroid bounding box
@@ -55,14 +53,14 @@ struct Rcb {
     if (ok(cr) && (best < 0 || std::abs(cr - m) < std::abs(best - m))) best = cr;
     if (best >= 0) m = best;
     if (n > (1 << 16)) {
-#pragma omp task firstprivate(lo, m)
-      run(lo, m);
-#pragma omp task firstprivate(m, hi)
-      run(m, hi);
+#pragma omp task firstprivate(lo, m, kl)
+      run(lo, m, kl);
+#pragma omp task firstprivate(m, hi, k, kl)
+      run(m, hi, k - kl);
 #pragma omp taskwait
     } else {
-      run(lo, m);
-      run(m, hi);
+      run(lo, m, kl);
+      run(m, hi, k - kl);
     }
   }
 };
@@ -70,7 +68,8 @@ struct Rcb {
 }  // namespace
 
 std::string build_tiling(int dim, int n_vert, int n_elem, const float* verts,
-                         const int32_t* elems, int tile_elems, Tiling& t, int n_halo, const int32_t* halo_verts) {
+                         const int32_t* elems, int tile_elems, Tiling& t, int n_halo, const int32_t* halo_verts,
+                         int wave) {
   if (dim != 2 && dim != 3) return "dim must be 2 or 3";
   if (n_vert <= 0 || n_elem <= 0) return "empty mesh";
   if (!verts || !elems) return "null mesh arrays";
@@ -102,9 +101,16 @@ std::string build_tiling(int dim, int n_vert, int n_elem, const float* verts,
     Rcb r;
     for (int a = 0; a < 3; ++a) r.c[a] = a < dim ? cen[a].data() : nullptr;
     r.dim = dim; r.T = tile_elems; r.idx = order.data(); r.is_start = &is_start;
+    // Tile count: ~88 % fill, so that cuts can snap to coordinate gaps (planar tile faces).  When the
+    // tile kernels run only a few waves of CTAs (wave = CTAs resident on the device; multi-GPU slabs),
+    // round the count up to whole waves of equal tiles: a 6.05-wave launch costs 7 tile times otherwise.
+    const int Tf = tile_elems - tile_elems / 8;
+    int k0 = std::max(1, (int)(((int64_t)n_elem + Tf - 1) / Tf));
+    if (wave > 0 && k0 >= wave && k0 < 64 * wave) k0 = (k0 + wave - 1) / wave * wave;
+    k0 = std::min(k0, n_elem);
 #pragma omp parallel
 #pragma omp single
-    r.run(0, n_elem);
+    r.run(0, n_elem, k0);
   }
   for (int a = 0; a < dim; ++a) std::vector<float>().swap(cen[a]);
   std::vector<int> tbeg;

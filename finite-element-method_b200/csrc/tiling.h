@@ -80,6 +80,6 @@ struct Tiling {
 // empty string on success, else an error message.
 std::string build_tiling(int dim, int n_vert, int n_elem, const float* verts,
                          const int32_t* elems, int tile_elems, Tiling& out, int n_halo = 0,
-                         const int32_t* halo_verts = nullptr);
+                         const int32_t* halo_verts = nullptr, int wave = 0);
 
 }  // namespace femb

@@ -26,7 +26,7 @@ EXPORTS = [
     "femb_object_create", "femb_object_destroy", "femb_object_info", "femb_set_stream", "femb_blocks_set",
     "femb_explicit_grad", "femb_energy_grad", "femb_kinematic", "femb_explicit_step", "femb_explicit_step_timed", "femb_implicit_solve",
     "femb_halo_bind", "femb_halo_mass", "femb_explicit_step_phase",
-    "femb_reduce_bind", "femb_implicit_solve_begin", "femb_implicit_solve_advance", "femb_implicit_solve_poll",
+    "femb_comm_bytes", "femb_peer_bind", "femb_peer_mass", "femb_reduce_bind", "femb_implicit_solve_begin", "femb_implicit_solve_advance", "femb_implicit_solve_poll",
     "femb_implicit_solve_finish",
     "femb_advect_implicit", "femb_implicit_assemble", "femb_implicit_apply", "femb_get", "femb_set",
     "femb_get_energy", "femb_sync", "femb_last_error", "femb_launch_count", "femb_version",
@@ -44,6 +44,12 @@ class Desc(C.Structure):
         ("n_halo", C.c_int32), ("halo_verts", C.POINTER(C.c_int32)),
         ("halo_owned", C.POINTER(C.c_uint8)),
     ]
+
+
+class PeerDesc(C.Structure):
+    _fields_ = [("rank", C.c_int32), ("world", C.c_int32), ("left", C.c_int32), ("right", C.c_int32),
+                ("n_left", C.c_int32), ("left_dst_off", C.c_int32), ("right_dst_off", C.c_int32),
+                ("recv_stride", C.c_int32), ("bufs", C.POINTER(C.c_void_p))]
 
 
 class Info(C.Structure):
@@ -90,6 +96,9 @@ def lib():
         "femb_halo_mass": (C.c_int, [vp, i32]),
         "femb_explicit_step_phase": (C.c_int, [vp, f32, fp, i32]),
         "femb_implicit_solve": (C.c_int, [vp, f32, i32, i32, i32, f32, ip, fp]),
+        "femb_comm_bytes": (C.c_int, [i32, C.POINTER(C.c_size_t), ip]),
+        "femb_peer_bind": (C.c_int, [vp, C.POINTER(PeerDesc)]),
+        "femb_peer_mass": (C.c_int, [vp]),
         "femb_reduce_bind": (C.c_int, [vp, vp]),
         "femb_implicit_solve_begin": (C.c_int, [vp, f32, i32, i32, i32, f32]),
         "femb_implicit_solve_advance": (C.c_int, [vp]),
@@ -264,6 +273,19 @@ class Handle:
         check(lib().femb_implicit_solve(self._h, float(dt), int(method), int(preconditioned), int(max_iter),
                                         float(tol), None, None))
 
+    # -- multi-GPU over peer memory: halo sums and dot products inside the library's kernels
+    def peer_bind(self, rank, world, left, right, n_left, left_dst_off, right_dst_off, recv_stride, buf_ptrs):
+        d = PeerDesc()
+        d.rank, d.world, d.left, d.right = int(rank), int(world), int(left), int(right)
+        d.n_left, d.left_dst_off, d.right_dst_off = int(n_left), int(left_dst_off), int(right_dst_off)
+        d.recv_stride = int(recv_stride)
+        arr = (C.c_void_p * world)(*[C.c_void_p(int(p)) for p in buf_ptrs])
+        d.bufs = C.cast(arr, C.POINTER(C.c_void_p))
+        check(lib().femb_peer_bind(self._h, C.byref(d)))
+
+    def peer_mass(self):
+        check(lib().femb_peer_mass(self._h))
+
     # -- the solve as segments between communication points (multi-GPU callers own the collectives)
     def reduce_bind(self, dev_ptr):
         check(lib().femb_reduce_bind(self._h, C.c_void_p(int(dev_ptr))))
@@ -308,6 +330,13 @@ class Handle:
 
     def sync(self):
         check(lib().femb_sync(self._h))
+
+
+def comm_bytes(max_halo):
+    """(bytes, recv_stride) of the comm buffer every rank must expose for halos of up to max_halo vertices."""
+    n, stride = C.c_size_t(), C.c_int32()
+    check(lib().femb_comm_bytes(int(max_halo), C.byref(n), C.byref(stride)))
+    return int(n.value), int(stride.value)
 
 
 def launch_count():

@@ -52,14 +52,70 @@ class SlabHalo:
         self.allred = None
         self.n = int(self.vertex_ids.size)
         self.send = self.recv = None
+        self.peer = False
         self._graphs = {}
 
-    def attach(self, handle, device=None):
-        """Allocate the send/recv buffers (torch, on the current CUDA device), bind them to the
-        library object and complete the lumped masses of the shared vertices."""
+    def attach_peer(self, handle):
+        """Peer-memory mode: one symmetric comm buffer per rank, mapped by every rank over NVLink
+        (torch symmetric memory); the library's own kernels then do the halo sums and the dot-product
+        sums with remote stores + flags -- no NCCL call on the data path.  Returns False (after telling
+        why on stderr) when symmetric memory cannot be set up; the caller then uses the NCCL path."""
+        import sys
+
+        import torch
+        import torch.distributed as dist
+
+        from . import _capi
+
+        self.torch = torch
+        try:
+            import torch.distributed._symmetric_memory as symm
+
+            plane = max(self.n_left, self.n_right)
+            nbytes, stride = _capi.comm_bytes(2 * plane)       # the same layout on every rank
+            if hasattr(symm, "enable_symm_mem_for_group"):
+                import warnings
+
+                with warnings.catch_warnings():
+                    warnings.simplefilter("ignore")
+                    symm.enable_symm_mem_for_group(dist.group.WORLD.group_name)
+            buf = symm.empty(nbytes, dtype=torch.uint8, device=torch.device("cuda", torch.cuda.current_device()))
+            buf.zero_()
+            torch.cuda.synchronize()
+            try:
+                hdl = symm.rendezvous(buf, dist.group.WORLD)
+            except TypeError:
+                hdl = symm.rendezvous(buf, dist.group.WORLD.group_name)
+            ptrs = [int(p) for p in hdl.buffer_ptrs]
+            dist.barrier()                                      # every rank's buffer is zeroed and mapped
+            torch.cuda.synchronize()
+        except Exception as ex:  # noqa: BLE001 -- any failure here just selects the NCCL path
+            print("femb200.dist: peer-memory mode unavailable (%s: %s); using NCCL" % (type(ex).__name__, ex),
+                  file=sys.stderr, flush=True)
+            return False
+        self._symm = (buf, hdl)                                 # keep the mapping alive
+        left = self.rank - 1 if self.n_left else -1
+        right = self.rank + 1 if self.n_right else -1
+        # my left plane is the left neighbour's RIGHT plane: it follows that rank's own left plane (if any)
+        left_dst_off = self.n_left if self.rank - 1 > 0 else 0
+        handle.peer_bind(self.rank, self.world, left, right, self.n_left, left_dst_off, 0, stride, ptrs)
+        handle.peer_mass()
+        dist.barrier()
+        self.peer = True
+        return True
+
+    def attach(self, handle, device=None, mode=None):
+        """Set up the halo machinery and complete the lumped masses of the shared vertices.
+        mode "peer": in-kernel communication over peer memory (default when available);
+        mode "nccl": send/recv buffers exchanged by torch.distributed P2P, scalars by all_reduce."""
+        import os
+
         import torch
 
         self.torch = torch
+        mode = mode or os.environ.get("FEMB200_COMM", "peer")
+        if mode == "peer" and self.world > 1 and self.attach_peer(handle):
+            return
         self.send = torch.zeros((self.n, 4), dtype=torch.float32, device=device or "cuda")
         self.recv = torch.zeros((self.n, 4), dtype=torch.float32, device=device or "cuda")
         handle.halo_bind(self.send.data_ptr(), self.recv.data_ptr())
@@ -95,6 +151,8 @@ class SlabHalo:
     def explicit_steps(self, handle, dt, g_dir, n, use_graph=True):
         """n fused explicit steps with a halo exchange in the middle of each.  The whole sequence
         (kernels + NCCL P2P) is captured once into a CUDA graph and replayed."""
+        if self.peer:                  # the library runs (and graph-captures) the whole sequence itself
+            return handle.explicit_step(dt, g_dir, n)
         torch = self.torch
         if not use_graph or n < 4:
             return self._steps_eager(handle, dt, g_dir, n)
@@ -145,6 +203,8 @@ class SlabHalo:
         into a CUDA graph and replayed; convergence is polled every few iterations."""
         from . import _capi
 
+        if self.peer:                  # halo sums and dot products happen inside the library's kernels
+            return handle.implicit_solve(dt, method, preconditioned, max_iter, tol, fetch=fetch)
         fixed = (tol == 0.0)
         n_cap = max_iter if max_iter > 0 else (500 if method == 1 else 20000)
         n_it = n_cap if method == 1 else n_cap + 2
@@ -185,7 +245,7 @@ class SlabHalo:
         """Drop the captured CUDA graphs (they hold NCCL work: the process group cannot be destroyed while
         they are alive)."""
         self._graphs.clear()
-        if self.send is not None and self.send.is_cuda:
+        if self.peer or (self.send is not None and self.send.is_cuda):
             self.torch.cuda.synchronize()
 
 

@@ -130,6 +130,25 @@ int femb_halo_mass(femb_object *obj, int32_t phase);
 /* one fused explicit step split around the exchange (phase 1 | exchange | phase 2) */
 int femb_explicit_step_phase(femb_object *obj, float dt, const float *g_dir, int32_t phase);
 
+/* ---- multi-GPU over peer memory (new).  Every rank allocates one comm buffer of femb_comm_bytes(max over
+ * ranks of n_halo) ZEROED bytes that all ranks can address (torch symmetric memory / CUDA IPC) and binds
+ * the table of mapped pointers.  From then on femb_explicit_step and femb_implicit_solve run the halo sums
+ * and the dot-product sums inside the library's own kernels over NVLink (remote stores + release/acquire
+ * flags): no collective call on the data path, and the whole step / iteration stays one CUDA graph.  Halo
+ * entries [0, n_left) belong to rank `left`, the rest to rank `right` (-1: none); *_dst_off = index of my
+ * plane inside that neighbour's halo list. */
+typedef struct femb_peer_desc {
+  int32_t rank, world;
+  int32_t left, right;
+  int32_t n_left;
+  int32_t left_dst_off, right_dst_off;
+  int32_t recv_stride;      /* from femb_comm_bytes, identical on all ranks */
+  void *const *bufs;        /* [world] comm buffer of every rank as mapped in THIS process */
+} femb_peer_desc;
+int femb_comm_bytes(int32_t max_halo, size_t *bytes_out, int32_t *recv_stride_out);
+int femb_peer_bind(femb_object *obj, const femb_peer_desc *desc);
+int femb_peer_mass(femb_object *obj); /* lumped masses of shared vertices, once after binding (synchronises) */
+
 /* ---- implicit path */
 /* implicit_solver_neo_hookean(obj), implicit.py:201-223, matrix-free.
  * method: 0 Jacobi (implicit.py:227-262), 1 CG (implicit.py:311-386);

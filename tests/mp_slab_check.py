@@ -95,6 +95,7 @@ def main():
                     ok = False
                     print("solve", name, "shared plane velocity differs between ranks", r, r + 1)
             print("solve", name, "iters slab/single", allr[0][name]["it"], it1, "resid", allr[0][name]["res"], res1)
+        print("COMM", "peer" if halo.peer else "nccl")
         print("SLAB_OK" if ok else "SLAB_FAIL")
     halo.close()
     h.close()

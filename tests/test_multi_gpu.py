@@ -160,12 +160,17 @@ def test_implicit_solve_driver_gloo_world2():
 
 
 @pytest.mark.gpu
-def test_two_rank_slabs_match_single_gpu():
+@pytest.mark.parametrize("comm", ["peer", "nccl"])
+def test_two_rank_slabs_match_single_gpu(comm):
+    """comm=peer: halo sums / dot products inside the library's kernels over NVLink peer memory;
+    comm=nccl: the same phases driven from Python with torch.distributed P2P + all_reduce."""
     import torch
 
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
+    env = dict(os.environ, FEMB200_COMM=comm)
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
                         "--master-addr", "127.0.0.1", "--master-port", "29611",
-                        os.path.join(ROOT, "tests", "mp_slab_check.py")], capture_output=True, text=True, timeout=180)
-    assert "SLAB_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+                        os.path.join(ROOT, "tests", "mp_slab_check.py")], capture_output=True, text=True, timeout=180,
+                       env=env)
+    assert "SLAB_OK" in r.stdout and ("COMM " + comm) in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
