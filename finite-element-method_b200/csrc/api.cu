@@ -1,6 +1,7 @@
 // api.cu -- the extern "C" surface of include/femb200.h: object lifetime, field
 // marshalling, explicit path.  (The implicit solve lives in api_solve.cu.)
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 #include "object.h"
@@ -146,7 +147,7 @@ int femb_object_create(const femb_desc* d, femb_object** out) {
     }
     o->dtl = DevTiling{d_tiles, d_lv, d_jds, d_rounds, d_bptr, t.n_tiles, t.n_interior, t.n_boundary, t.n_vert,
                        t.n_slots, (t.max_tile_elems + 31) / 32 * 32, t.max_lv, (t.max_rounds + 3) / 4 * 4, t.nc,
-                       prop.multiProcessorCount * occ, grid, d_bskip};
+                       prop.multiProcessorCount * occ, grid, t.n_halo_tiles, d_bskip};
 
     const size_t ns = (size_t)t.n_slots, nv = (size_t)t.n_vert;
     o->e.p0 = o->alloc<float4>(ns);
@@ -197,6 +198,9 @@ int femb_object_destroy(femb_object* o) {
   if (o->solve_graph.exec) cudaGraphExecDestroy(o->solve_graph.exec);
   for (void* p : o->allocs) cudaFree(p);
   if (o->h_sc) cudaFreeHost(o->h_sc);
+  if (o->side) { cudaStreamSynchronize(o->side); cudaStreamDestroy(o->side); }
+  if (o->ev_fork) cudaEventDestroy(o->ev_fork);
+  if (o->ev_join) cudaEventDestroy(o->ev_join);
   if (o->own_stream && o->stream) cudaStreamDestroy(o->stream);
   cudaGetLastError();
   delete o;
@@ -307,13 +311,9 @@ int femb_explicit_step(femb_object* o, float dt, const float* g_dir, int32_t n_s
         continue;
       }
       // slab rank: tile kernel | shared-vertex sums straight into the neighbours' memory | boundary kernel
-      LaunchCfg c1 = o->cfg, c2 = o->cfg;
-      c1.phase = 1; c2.phase = 2;
-      launch_explicit(o->dim, EX_STEP, c1, o->dtl, o->e, o->vs, o->mat, kin, nullptr, nullptr);
-      launch_halo_send(c1, o->dtl, o->peer, o->halo, o->vs.partial, o->vs.pos, 0);
-      launch_halo_recv(c2, o->dtl, o->peer, o->halo, o->vs.partial, o->vs.pos, 0);
-      o->halo_dirty = true;
-      launch_explicit(o->dim, EX_STEP, c2, o->dtl, o->e, o->vs, o->mat, kin, nullptr, nullptr);
+      o->peer_pass([&](const LaunchCfg& c) {
+        launch_explicit(o->dim, EX_STEP, c, o->dtl, o->e, o->vs, o->mat, kin, nullptr, nullptr);
+      });
     }
   };
   // (the legacy default stream cannot be captured)
@@ -421,6 +421,15 @@ int femb_peer_bind(femb_object* o, const femb_peer_desc* d) {
   if (d->recv_stride < o->halo.n) throw ArgError("recv_stride must be the value femb_comm_bytes returned for the largest halo");
   pc.recv_stride = (size_t)d->recv_stride;   // common to all ranks: remote addresses are computed with it
   pc.st = o->alloc<CommState>(1);
+  if (!o->side) {
+    // highest priority: when the halo tiles finish, the (small) send kernel gets SM slots before the
+    // CTAs of the other tiles fill the device
+    int prio_lo = 0, prio_hi = 0;
+    FEMB_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    FEMB_CUDA(cudaStreamCreateWithPriority(&o->side, cudaStreamNonBlocking, prio_hi));
+    FEMB_CUDA(cudaEventCreateWithFlags(&o->ev_fork, cudaEventDisableTiming));
+    FEMB_CUDA(cudaEventCreateWithFlags(&o->ev_join, cudaEventDisableTiming));
+  }
   o->d_allred_own = o->alloc<double>(1);
   o->d_allred = o->d_allred_own;
   FEMB_CUDA(cudaStreamSynchronize(o->stream));

@@ -26,7 +26,9 @@ int fail(const std::exception& ex);
   }                                  \
   return FEMB_OK;
 
-static int apply_red_slots(const femb_object* o) { return apply_tile_grid(o->dtl) + (o->dtl.n_boundary + 255) / 256; }
+static int apply_red_slots(const femb_object* o) {
+  return apply_tile_grid(o->dtl, o->pass_split()) + (o->dtl.n_boundary + 255) / 256;
+}
 
 static void poll(femb_object* o) {
   FEMB_CUDA(cudaMemcpyAsync(o->h_sc, o->d_sc, sizeof(SolveScalars), cudaMemcpyDeviceToHost, o->stream));
@@ -46,7 +48,7 @@ static void assemble(femb_object* o, float dt, bool with_diag) {
 namespace {
 
 using PassFn = std::function<void(const LaunchCfg&)>;
-using SumFn = std::function<void(int, const double*)>;
+using SumFn = std::function<void(int, const double*, const PeerComm&)>;
 
 struct Builder {
   femb_object* o;
@@ -63,15 +65,7 @@ struct Builder {
       return;
     }
     if (ob->peer_on) {   // halo sums through peer memory, inside our own kernels: no communication point
-      add([ob, f] {
-        LaunchCfg c1 = ob->cfg, c2 = ob->cfg;
-        c1.phase = 1; c2.phase = 2;
-        f(c1);
-        launch_halo_send(c1, ob->dtl, ob->peer, ob->halo, ob->vs.partial, ob->vs.pos, 0);
-        launch_halo_recv(c2, ob->dtl, ob->peer, ob->halo, ob->vs.partial, ob->vs.pos, 0);
-        ob->halo_dirty = true;
-        f(c2);
-      });
+      add([ob, f] { ob->peer_pass(f); });
       return;
     }
     add([ob, f] {
@@ -94,19 +88,18 @@ struct Builder {
   void gsum(int n_red, SumFn consume) {
     femb_object* ob = o;
     if (!dist) {
-      add([ob, n_red, consume] { consume(n_red, ob->d_red); });
+      add([ob, n_red, consume] { consume(n_red, ob->d_red, PeerComm{}); });
       return;
     }
     if (ob->peer_on) {
       add([ob, n_red, consume] {
-        launch_reduce_final(ob->cfg, n_red, ob->d_red, ob->d_allred);
-        launch_allsum(ob->cfg, ob->peer, ob->d_allred);
-        consume(1, ob->d_allred);
+        launch_reduce_final_send(ob->cfg, n_red, ob->d_red, ob->peer);   // my partial -> every rank's slot
+        consume(0, nullptr, ob->peer);                                     // gathers the slots, then the scalar math
       });
       return;
     }
     add([ob, n_red] { launch_reduce_final(ob->cfg, n_red, ob->d_red, ob->d_allred); }, FEMB_COMM_ALLREDUCE);
-    add([ob, consume] { consume(1, ob->d_allred); });
+    add([ob, consume] { consume(1, ob->d_allred, PeerComm{}); });
   }
 };
 
@@ -152,7 +145,7 @@ void build_program(femb_object* o, SolveProgram& P, float dt, int method, int pr
       pro.pass(apply(0, iv.b, iv.q, AP_PLAIN, nullptr, nullptr, nullptr));
     }
     pro.add([=] { launch_cg_init(o->cfg, nv, iv, rhs, iv.q, o->d_red, mask); });   // x = b, r = rhs - op(x), d = r
-    pro.gsum(vred, [=](int n, const double* red) { launch_cg_delta0(o->cfg, n, red, sc, ktol, max_iter); });
+    pro.gsum(vred, [=](int n, const double* red, const PeerComm& pc) { launch_cg_delta0(o->cfg, n, red, sc, ktol, max_iter, pc); });
 
     if (preconditioned == 1) {
       it.pass(apply(0, iv.d, iv.tmp, AP_PLAIN, nullptr, nullptr, sc));
@@ -160,16 +153,16 @@ void build_program(femb_object* o, SolveProgram& P, float dt, int method, int pr
     } else {
       it.pass(apply(0, iv.d, iv.q, AP_DOT, iv.d, nullptr, sc));
     }
-    it.gsum(ared, [=](int n, const double* red) { launch_cg_alpha(o->cfg, n, red, sc); });
+    it.gsum(ared, [=](int n, const double* red, const PeerComm& pc) { launch_cg_alpha(o->cfg, n, red, sc, pc); });
     it.add([=] { launch_cg_update_xr(o->cfg, nv, iv, o->d_red, sc, mask); });
-    it.gsum(vred, [=](int n, const double* red) { launch_cg_beta(o->cfg, n, red, sc, ktol, max_iter); });
+    it.gsum(vred, [=](int n, const double* red, const PeerComm& pc) { launch_cg_beta(o->cfg, n, red, sc, ktol, max_iter, pc); });
     it.add([=] { launch_cg_update_d(o->cfg, nv, iv, sc); });
   } else {
     // ---- the reference's damped "Jacobi" (227-262, 391-404) as a true parallel Jacobi
     pro.pass([o, dim, dt](const LaunchCfg& c) { launch_implicit_diag(dim, c, o->dtl, o->h, o->vs, dt, o->iv); });
     pro.add([=] { launch_scale_xyz(o->cfg, nv, iv.b, iv.x, 0.5f); });               // x0 = 0.5 b (231-232)
     it.pass(apply(0, iv.x, iv.tmp, AP_RESID, iv.b, iv.r, sc));
-    it.gsum(ared, [=](int n, const double* red) { launch_jacobi_decide(o->cfg, n, red, sc, tol, max_iter, fixed); });
+    it.gsum(ared, [=](int n, const double* red, const PeerComm& pc) { launch_jacobi_decide(o->cfg, n, red, sc, tol, max_iter, fixed, pc); });
     it.add([=] { launch_jacobi_update(o->cfg, nv, iv, sc); });
   }
 }

@@ -1,0 +1,63 @@
+// comm.cuh -- device-side primitives of the peer-memory communication (see kernels_comm.cu).
+#pragma once
+#include "launch.h"
+
+namespace femb {
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+constexpr long long kSpinLimit = 20000000000ll;   // ~10 s at 2 GHz
+
+// wait until *flag >= seq (flags only grow); false on time-out
+__device__ __forceinline__ bool spin_until(const uint32_t* flag, uint32_t seq, CommState* st) {
+  const long long t0 = clock64();
+  while ((int32_t)(ld_acquire_sys(flag) - seq) < 0) {
+    if (clock64() - t0 > kSpinLimit) {
+      st->error = 1;
+      return false;
+    }
+    __nanosleep(64);
+  }
+  return true;
+}
+
+__device__ __forceinline__ CommHeader* hdr_of(char* base) { return reinterpret_cast<CommHeader*>(base); }
+__device__ __forceinline__ float4* recv_of(char* base, const PeerComm& pc, uint32_t parity) {
+  return reinterpret_cast<float4*>(base + pc.recv_off) + (size_t)parity * pc.recv_stride;
+}
+
+// this rank's partial `v` -> slot[rank] of every rank, then the flag (lanes 0..world-1 of one warp)
+__device__ __forceinline__ void allsum_scatter(const PeerComm& pc, double v, int lane) {
+  const uint32_t seq = pc.st->ar_seq + 1, parity = seq & 1u;
+  if (lane < pc.world) {
+    double* slot = reinterpret_cast<double*>(pc.all[lane] + pc.slot_off) + parity * kMaxRanks + pc.rank;
+    *slot = v;
+    __threadfence_system();
+    st_release_sys(&hdr_of(pc.all[lane])->ar_flag[pc.rank], seq);
+  }
+}
+
+// wait for every rank's slot and sum them in rank order (identical bits on all ranks).  Called by one full
+// warp; the result is valid in lane 0.  Always consumes one sequence number.
+__device__ __forceinline__ double allsum_gather(const PeerComm& pc, int lane) {
+  CommState* st = pc.st;
+  const uint32_t seq = st->ar_seq + 1, parity = seq & 1u;
+  if (lane < pc.world) spin_until(&hdr_of(pc.self)->ar_flag[lane], seq, st);
+  __syncwarp();
+  double s = 0.0;
+  if (lane == 0) {
+    const double* slot = reinterpret_cast<const double*>(pc.self + pc.slot_off) + parity * kMaxRanks;
+    for (int i = 0; i < pc.world; ++i) s += __ldcv(slot + i);
+    st->ar_seq = seq;
+  }
+  return s;
+}
+
+}  // namespace femb

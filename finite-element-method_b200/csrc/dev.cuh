@@ -42,6 +42,7 @@ struct DevTiling {
   int nc;                // corners per element (dim + 1)
   int prefetch_dist;     // tiles ahead whose element planes are prefetched into L2 (0 = off)
   int grid;              // CTAs of the persistent tile kernels (SM slots)
+  int n_halo_tiles;      // multi-GPU: tiles [0, n_halo_tiles) touch a vertex shared with another rank
   const uint8_t* bskip;  // [n_boundary] multi-GPU: 1 = shared vertex counted by ANOTHER rank in global
                          // reductions (dots, norms); nullptr on single-GPU objects
 };

@@ -16,38 +16,10 @@
 // so a lost peer cannot hang the GPU; the host turns the flag into an error at the next sync.
 #include <stdexcept>
 
+#include "comm.cuh"
 #include "launch.h"
 
 namespace femb {
-
-__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
-  uint32_t v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-
-constexpr long long kSpinLimit = 20000000000ll;   // ~10 s at 2 GHz
-
-// wait until *flag >= seq (flags only grow); false on time-out
-__device__ __forceinline__ bool spin_until(const uint32_t* flag, uint32_t seq, CommState* st) {
-  const long long t0 = clock64();
-  while ((int32_t)(ld_acquire_sys(flag) - seq) < 0) {
-    if (clock64() - t0 > kSpinLimit) {
-      st->error = 1;
-      return false;
-    }
-    __nanosleep(64);
-  }
-  return true;
-}
-
-__device__ __forceinline__ CommHeader* hdr_of(char* base) { return reinterpret_cast<CommHeader*>(base); }
-__device__ __forceinline__ float4* recv_of(char* base, const PeerComm& pc, uint32_t parity) {
-  return reinterpret_cast<float4*>(base + pc.recv_off) + (size_t)parity * pc.recv_stride;
-}
 
 // what == 0: send[k] = sum of the local partial slots of halo vertex k (same order as k_boundary)
 // what == 1: send[k] = {lumped mass of vertex k, 0, 0, 0}
@@ -71,9 +43,11 @@ __global__ void __launch_bounds__(256) k_halo_send(PeerComm pc, int n, const int
     if (k < pc.n_left) recv_of(pc.left, pc, parity)[pc.left_dst_off + k] = s;
     else recv_of(pc.right, pc, parity)[pc.right_dst_off + (k - pc.n_left)] = s;
   }
-  __threadfence_system();
+  // release pattern of a grid barrier: CTA barrier, then ONE system-scope fence (cumulative over the stores
+  // the barrier ordered before it) -- a fence per thread would wait for an NVLink round trip 256 times
   __syncthreads();
   if (threadIdx.x == 0) {
+    __threadfence_system();
     const unsigned prev = atomicAdd(&st->pack_count, 1u);
     if (prev == gridDim.x - 1) {            // last CTA: every remote store of this kernel is fenced
       st->pack_count = 0;
@@ -113,35 +87,6 @@ __global__ void __launch_bounds__(256) k_halo_recv(PeerComm pc, int n, const int
   }
 }
 
-// local partial sum -> slot[rank] of every rank, then the flag
-__global__ void __launch_bounds__(32) k_allsum_send(PeerComm pc, const double* local) {
-  CommState* st = pc.st;
-  const uint32_t seq = st->ar_seq + 1, parity = seq & 1u;
-  const int r = threadIdx.x;
-  if (r < pc.world) {
-    double* slot = reinterpret_cast<double*>(pc.all[r] + pc.slot_off) + parity * kMaxRanks + pc.rank;
-    *slot = *local;
-    __threadfence_system();
-    st_release_sys(&hdr_of(pc.all[r])->ar_flag[pc.rank], seq);
-  }
-}
-
-// wait for every rank's slot, sum in rank order
-__global__ void __launch_bounds__(32) k_allsum_wait(PeerComm pc, double* out) {
-  CommState* st = pc.st;
-  const uint32_t seq = st->ar_seq + 1, parity = seq & 1u;
-  const int r = threadIdx.x;
-  if (r < pc.world) spin_until(&hdr_of(pc.self)->ar_flag[r], seq, st);
-  __syncwarp();
-  if (r == 0) {
-    const double* slot = reinterpret_cast<const double*>(pc.self + pc.slot_off) + parity * kMaxRanks;
-    double s = 0.0;
-    for (int i = 0; i < pc.world; ++i) s += __ldcv(slot + i);
-    *out = s;
-    st->ar_seq = seq;
-  }
-}
-
 static inline int nblk(int n) { return (n + 255) / 256; }
 
 void launch_halo_send(const LaunchCfg& c, const DevTiling& tl, const PeerComm& pc, Halo h, const float4* partial,
@@ -156,13 +101,6 @@ void launch_halo_recv(const LaunchCfg& c, const DevTiling& tl, const PeerComm& p
   k_halo_recv<<<nblk(h.n), 256, 0, c.stream>>>(pc, h.n, h.b, tl.bptr, partial, pos, tl.n_interior, what);
   note_launch("halo_recv", c.stream);
 }
-void launch_allsum(const LaunchCfg& c, const PeerComm& pc, double* value) {
-  k_allsum_send<<<1, 32, 0, c.stream>>>(pc, value);
-  note_launch("allsum_send", c.stream);
-  k_allsum_wait<<<1, 32, 0, c.stream>>>(pc, value);
-  note_launch("allsum_wait", c.stream);
-}
-
 size_t comm_layout(int n_halo, size_t* recv_off, size_t* slot_off, size_t* recv_stride) {
   size_t off = sizeof(CommHeader);
   *slot_off = off;

@@ -9,6 +9,7 @@
 // evaluates its convergence test in-kernel, implicit.py:252,341).
 #include <stdexcept>
 
+#include "comm.cuh"
 #include "launch.h"
 #include "tile_pass.cuh"
 
@@ -49,6 +50,14 @@ __device__ double final_sum(const double* red, int n) {
   return s[0];
 }
 
+// The global sum a scalar kernel consumes: single GPU -> the per-CTA partials red[0..n); multi-GPU over peer
+// memory (pc.st != nullptr) -> every rank's already-reduced partial, gathered through the comm buffers.
+// Result valid in thread 0.  In peer mode a sequence number is consumed on every call, `done` or not.
+__device__ double global_sum(const double* red, int n, const PeerComm& pc) {
+  if (pc.st == nullptr) return final_sum(red, n);
+  return threadIdx.x < 32 ? allsum_gather(pc, threadIdx.x) : 0.0;
+}
+
 __global__ void k_scalars_reset(SolveScalars* sc) {
   SolveScalars z = {};
   z.first = 1;
@@ -76,9 +85,10 @@ __global__ void __launch_bounds__(256) k_cg_init(int n, ImplicitVecs iv, const f
 // kind 0: delta_new = sum (loop entry test) ; kind 1: alpha = delta_new / (d.q) ;
 // kind 2: delta_old = delta_new, delta_new = sum, beta, ++iters, loop test   (implicit.py:341,354,378-386)
 __global__ void __launch_bounds__(kFinalThreads) k_cg_scalar(int kind, int n_red, const double* red, SolveScalars* sc, float tol,
-                                                   int max_iter) {
+                                                   int max_iter, PeerComm pc) {
+  if (pc.st == nullptr && sc->done) return;
+  const double s = global_sum(red, n_red, pc);
   if (sc->done) return;
-  const double s = final_sum(red, n_red);
   if (threadIdx.x != 0) return;
   if (kind == 0) {
     sc->delta_new = s;
@@ -132,13 +142,14 @@ __global__ void __launch_bounds__(256) k_cg_update_d(int n, ImplicitVecs iv, con
 
 // Jacobi control flow, implicit.py:234-261, from err = ||b - A x|| of the CURRENT iterate.
 __global__ void __launch_bounds__(kFinalThreads) k_jacobi_decide(int n_red, const double* red, SolveScalars* sc, float tol,
-                                                       int max_iter, int fixed) {
+                                                       int max_iter, int fixed, PeerComm pc) {
+  if (pc.st == nullptr && sc->done) return;
+  const double s = global_sum(red, n_red, pc);
   if (sc->done) return;
   if (sc->terminal) {
     if (threadIdx.x == 0) sc->done = 1;
     return;
   }
-  const double s = final_sum(red, n_red);
   if (threadIdx.x != 0) return;
   const float err = sqrtf((float)s);
   int action = JA_NONE;
@@ -231,6 +242,15 @@ __global__ void __launch_bounds__(kFinalThreads) k_reduce_final(int n_red, const
   if (threadIdx.x == 0) *out = s;
 }
 
+// local sum of the per-CTA partials -> slot[rank] of every rank (peer memory), in one kernel
+__global__ void __launch_bounds__(kFinalThreads) k_reduce_final_send(int n_red, const double* red, PeerComm pc) {
+  __shared__ double s_v;
+  const double s = final_sum(red, n_red);
+  if (threadIdx.x == 0) s_v = s;
+  __syncthreads();
+  if (threadIdx.x < 32) allsum_scatter(pc, s_v, threadIdx.x);
+}
+
 // dst[old*ncomp + k] = src[new_of_old[old]].comp[comp0 + k]
 __global__ void __launch_bounds__(256) k_pack_vertex(int n, const int32_t* new_of_old, const float4* src, int comp0,
                                                      int ncomp, float* dst) {
@@ -293,20 +313,22 @@ void launch_cg_init(const LaunchCfg& c, int n_vert, ImplicitVecs iv, const float
   k_cg_init<<<nblk(n_vert), 256, 0, c.stream>>>(n_vert, iv, rhs, opx, red, mask);
   note_launch("cg_init", c.stream);
 }
-void launch_cg_delta0(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc, float tol, int max_iter) {
-  k_cg_scalar<<<1, kFinalThreads, 0, c.stream>>>(0, n_red, red, sc, tol, max_iter);
+void launch_cg_delta0(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc, float tol, int max_iter,
+                      const PeerComm& pc) {
+  k_cg_scalar<<<1, kFinalThreads, 0, c.stream>>>(0, n_red, red, sc, tol, max_iter, pc);
   note_launch("cg_scalar0", c.stream);
 }
-void launch_cg_alpha(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc) {
-  k_cg_scalar<<<1, kFinalThreads, 0, c.stream>>>(1, n_red, red, sc, 0.f, 0);
+void launch_cg_alpha(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc, const PeerComm& pc) {
+  k_cg_scalar<<<1, kFinalThreads, 0, c.stream>>>(1, n_red, red, sc, 0.f, 0, pc);
   note_launch("cg_alpha", c.stream);
 }
 void launch_cg_update_xr(const LaunchCfg& c, int n_vert, ImplicitVecs iv, double* red, SolveScalars* sc, RedMask mask) {
   k_cg_update_xr<<<nblk(n_vert), 256, 0, c.stream>>>(n_vert, iv, red, sc, mask);
   note_launch("cg_update_xr", c.stream);
 }
-void launch_cg_beta(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc, float tol, int max_iter) {
-  k_cg_scalar<<<1, kFinalThreads, 0, c.stream>>>(2, n_red, red, sc, tol, max_iter);
+void launch_cg_beta(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc, float tol, int max_iter,
+                    const PeerComm& pc) {
+  k_cg_scalar<<<1, kFinalThreads, 0, c.stream>>>(2, n_red, red, sc, tol, max_iter, pc);
   note_launch("cg_beta", c.stream);
 }
 void launch_cg_update_d(const LaunchCfg& c, int n_vert, ImplicitVecs iv, const SolveScalars* sc) {
@@ -314,8 +336,8 @@ void launch_cg_update_d(const LaunchCfg& c, int n_vert, ImplicitVecs iv, const S
   note_launch("cg_update_d", c.stream);
 }
 void launch_jacobi_decide(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc, float tol,
-                          int max_iter, int fixed) {
-  k_jacobi_decide<<<1, kFinalThreads, 0, c.stream>>>(n_red, red, sc, tol, max_iter, fixed);
+                          int max_iter, int fixed, const PeerComm& pc) {
+  k_jacobi_decide<<<1, kFinalThreads, 0, c.stream>>>(n_red, red, sc, tol, max_iter, fixed, pc);
   note_launch("jacobi_decide", c.stream);
 }
 void launch_jacobi_update(const LaunchCfg& c, int n_vert, ImplicitVecs iv, SolveScalars* sc) {
@@ -337,6 +359,10 @@ void launch_fill(const LaunchCfg& c, int n, float4* dst, float4 v) {
 void launch_reduce_final(const LaunchCfg& c, int n_red, const double* red, double* out) {
   k_reduce_final<<<1, kFinalThreads, 0, c.stream>>>(n_red, red, out);
   note_launch("reduce_final", c.stream);
+}
+void launch_reduce_final_send(const LaunchCfg& c, int n_red, const double* red, const PeerComm& pc) {
+  k_reduce_final_send<<<1, kFinalThreads, 0, c.stream>>>(n_red, red, pc);
+  note_launch("reduce_final_send", c.stream);
 }
 void launch_pack_vertex(const LaunchCfg& c, int, int n_vert, const int32_t* new_of_old, const float4* src, int comp0,
                         int ncomp, float* dst) {

@@ -49,6 +49,8 @@ struct LaunchCfg {
   cudaEvent_t ev_mid = nullptr;  // if set, recorded between the tile and the boundary kernel of a pass
   int phase = 0;                 // 0: tile + boundary kernel; 1: tile kernel only; 2: boundary kernel only
                                  // (multi-GPU: the halo exchange of the partial sums runs between 1 and 2)
+  int part = 0;                  // phase 1 only -- 0: all tiles; 1: the halo tiles [0, n_halo_tiles);
+                                 // 2: the other tiles (the exchange overlaps part 2)
 };
 
 struct Halo {                    // vertices shared with a neighbouring rank (slab interface planes)
@@ -84,8 +86,8 @@ void launch_halo_send(const LaunchCfg& c, const DevTiling& tl, const PeerComm& p
                       const float4* pos, int what);
 void launch_halo_recv(const LaunchCfg& c, const DevTiling& tl, const PeerComm& pc, Halo h, float4* partial,
                       float4* pos, int what);
-// *value = sum over ranks of *value, identical bits on every rank
-void launch_allsum(const LaunchCfg& c, const PeerComm& pc, double* value);
+// local sum of red[0..n_red) -> slot[rank] of every rank; the consuming scalar kernel gathers the slots
+void launch_reduce_final_send(const LaunchCfg& c, int n_red, const double* red, const PeerComm& pc);
 
 // send[k] = sum of the local partial slots of halo vertex k ; partial[remote slot of k] = recv[k]
 void launch_halo_pack(const LaunchCfg& c, const DevTiling& tl, Halo h, const float4* partial);
@@ -113,7 +115,7 @@ void launch_apply(int dim, const LaunchCfg& c, const DevTiling& tl, Planes h, Ve
                   int transpose, const float4* in, float4* out, int epilogue, const float4* aux,
                   float4* resid_out, double* red, const SolveScalars* sc);
 int reduce_slots(const DevTiling& tl, const LaunchCfg& c);
-int apply_tile_grid(const DevTiling& tl);   // per-CTA reduction partials written by an operator pass
+int apply_tile_grid(const DevTiling& tl, bool split = false);   // per-CTA reduction partials written by an operator pass
 int energy_tile_grid(const DevTiling& tl);  // ... by the energy pass  // doubles needed in a reduction buffer
 
 // CG / Jacobi vector kernels (all early-exit on sc->done)
@@ -125,13 +127,15 @@ struct RedMask {           // which vertices this rank counts in global reductio
 void launch_cg_init(const LaunchCfg& c, int n_vert, ImplicitVecs iv, const float4* rhs, const float4* opx,
                     double* red, RedMask mask);
 // delta_new = sum red[0..n_red), loop entry test
-void launch_cg_delta0(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc, float tol, int max_iter);
-void launch_cg_alpha(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc);
+void launch_cg_delta0(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc, float tol, int max_iter,
+                      const PeerComm& pc);
+void launch_cg_alpha(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc, const PeerComm& pc);
 void launch_cg_update_xr(const LaunchCfg& c, int n_vert, ImplicitVecs iv, double* red, SolveScalars* sc, RedMask mask);
-void launch_cg_beta(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc, float tol, int max_iter);
+void launch_cg_beta(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc, float tol, int max_iter,
+                    const PeerComm& pc);
 void launch_cg_update_d(const LaunchCfg& c, int n_vert, ImplicitVecs iv, const SolveScalars* sc);
 void launch_jacobi_decide(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc, float tol,
-                          int max_iter, int fixed);
+                          int max_iter, int fixed, const PeerComm& pc);
 void launch_jacobi_update(const LaunchCfg& c, int n_vert, ImplicitVecs iv, SolveScalars* sc);
 void launch_scalars_reset(const LaunchCfg& c, SolveScalars* sc);
 

@@ -120,6 +120,38 @@ struct femb_object {
     if (zero) FEMB_CUDA(cudaMemsetAsync(p, 0, bytes, stream));
     return static_cast<T*>(p);
   }
+  cudaStream_t side = nullptr;      // peer mode: the halo send runs here, overlapping the non-halo tiles
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  bool pass_split() const { return peer_on && side && dtl.n_halo_tiles > 0 && dtl.n_halo_tiles < dtl.n_tiles; }
+  // One tile pass of a slab rank over peer memory.  f(cfg) launches the pass's kernels for the phase / part
+  // in cfg:   halo tiles | send (side stream) || other tiles | wait for the neighbours | boundary kernel
+  template <class F>
+  void peer_pass(F f) {
+    using namespace femb;
+    LaunchCfg c1 = cfg, c2 = cfg;
+    c1.phase = 1;
+    c2.phase = 2;
+    if (pass_split()) {
+      c1.part = 1;
+      f(c1);
+      FEMB_CUDA(cudaEventRecord(ev_fork, stream));
+      FEMB_CUDA(cudaStreamWaitEvent(side, ev_fork, 0));
+      LaunchCfg cs = cfg;
+      cs.stream = side;
+      launch_halo_send(cs, dtl, peer, halo, vs.partial, vs.pos, 0);
+      FEMB_CUDA(cudaEventRecord(ev_join, side));
+      c1.part = 2;
+      f(c1);
+      FEMB_CUDA(cudaStreamWaitEvent(stream, ev_join, 0));
+      c2.part = 1;   // tells the boundary kernel where the tile partials of a split pass end
+    } else {
+      f(c1);
+      launch_halo_send(c1, dtl, peer, halo, vs.partial, vs.pos, 0);
+    }
+    launch_halo_recv(c2, dtl, peer, halo, vs.partial, vs.pos, 0);
+    halo_dirty = true;
+    f(c2);
+  }
   // a peer wait that timed out leaves CommState.error set: surface it (call after a stream sync)
   void check_comm_error() {
     if (!peer_on) return;

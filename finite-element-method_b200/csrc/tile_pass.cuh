@@ -162,15 +162,16 @@ __device__ __forceinline__ void gather_local_vertex(int n_rounds, const uint32_t
 //   before the gather of t : vertex values of t' requested into registers (their table has landed)
 //   next iteration  : registers -> shared memory, first element loads already issued.
 template <int D, class Op>
-__global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile_persistent(DevTiling tl, typename Op::Args a) {
+__global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile_persistent(DevTiling tl, typename Op::Args a, int t_begin,
+                                                                           int t_end, int red_off) {
   extern __shared__ float4 smem4[];
   __shared__ float s_warp[32];
   __shared__ uint64_t s_bar[3];          // [0],[1]: descriptor + local-vertex table buffers; [2]: JDS lists
   __shared__ __align__(16) DevTile s_td[2];
   grid_launch_dependents();
   if (Op::early_exit(a)) return;
-  int t = blockIdx.x;
-  if (t >= tl.n_tiles) return;
+  int t = t_begin + blockIdx.x;
+  if (t >= t_end) return;
   constexpr int S = kStride;
   const TileSmem lay = tile_smem_layout(tl.max_lv, tl.max_rounds, tl.nc, n_planes<D, Op>());
   char* smem = reinterpret_cast<char*>(smem4);
@@ -210,7 +211,7 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile_persistent(Dev
     const LocalVert* s_lv = lv_buf(b);
     const int n_elem = td.n_elem, slot_off = td.slot_off;
     const int tn = t + G;
-    const bool has_next = tn < tl.n_tiles;
+    const bool has_next = tn < t_end;
     if (tid == 0) {
       const uint32_t r_bytes = (uint32_t)round_up(td.n_rounds * 4, 16);
       const uint32_t j_bytes = (uint32_t)round_up(td.n_elem * tl.nc * 2, 16);
@@ -285,19 +286,21 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile_persistent(Dev
   }
   if (Op::REDUCE) {
     const float r = block_sum(red, s_warp);
-    if (tid == 0) Op::red_buf(a)[blockIdx.x] = (double)r;
+    if (tid == 0) Op::red_buf(a)[red_off + blockIdx.x] = (double)r;
   }
 }
 
 // One CTA per tile.
 template <int D, class Op>
-__global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile(DevTiling tl, typename Op::Args a) {
+__global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile(DevTiling tl, typename Op::Args a, int t_begin, int t_end,
+                                                               int red_off) {
   extern __shared__ float4 smem4[];
   __shared__ float s_warp[32];
   __shared__ uint64_t s_bar[2];   // [0]: local-vertex table landed, [1]: JDS lists landed
   grid_launch_dependents();
   if (Op::early_exit(a)) return;
-  const DevTile td = tl.tiles[blockIdx.x];
+  const int tile = t_begin + blockIdx.x;
+  const DevTile td = tl.tiles[tile];
   constexpr int S = kStride;
   const TileSmem lay = tile_smem_layout(tl.max_lv, tl.max_rounds, tl.nc, n_planes<D, Op>());
   char* smem = reinterpret_cast<char*>(smem4);
@@ -320,8 +323,8 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile(DevTiling tl, 
     bulk_g2s(s_rounds, tl.rounds + td.rounds_off, r_bytes, &s_bar[1]);
     bulk_g2s(s_jds, tl.jds + td.jds_off, j_bytes, &s_bar[1]);
     // L2 prefetch of the tile that will occupy this SM slot after us
-    const int nxt = blockIdx.x + tl.prefetch_dist;
-    if (tl.prefetch_dist > 0 && nxt < tl.n_tiles) {
+    const int nxt = tile + tl.prefetch_dist;
+    if (tl.prefetch_dist > 0 && nxt < t_end) {
       const DevTile tn = tl.tiles[nxt];
       Op::prefetch(a, tn.slot_off, (uint32_t)(round_up(tn.n_elem, 32) * 16));
       bulk_prefetch_l2(tl.lv + tn.lv_off, (uint32_t)round_up(tn.n_lv * 8, 16));
@@ -377,7 +380,7 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile(DevTiling tl, 
   }
   if (Op::REDUCE) {
     const float r = block_sum(red, s_warp);
-    if (threadIdx.x == 0) Op::red_buf(a)[blockIdx.x] = (double)r;
+    if (threadIdx.x == 0) Op::red_buf(a)[red_off + blockIdx.x] = (double)r;
   }
 }
 constexpr int kBoundaryBlock = 256;
@@ -431,9 +434,15 @@ __device__ __forceinline__ void prefetch_planes(const Planes& p, int slot, uint3
   if (three) bulk_prefetch_l2(p.p2 + slot, bytes);
 }
 
-// CTAs of the tile kernel of an Op == number of per-CTA reduction partials it writes
+// CTAs the tile kernel of an Op uses for `n` tiles == per-CTA reduction partials it writes
 template <class Op>
-inline int tile_grid(const DevTiling& tl) { return Op::PERSIST ? tl.grid : tl.n_tiles; }
+inline int tile_ctas(const DevTiling& tl, int n) { return Op::PERSIST ? (n < tl.grid ? n : tl.grid) : n; }
+// partials of a whole pass; split: the pass is launched as halo tiles + other tiles (multi-GPU overlap)
+template <class Op>
+inline int tile_grid(const DevTiling& tl, bool split = false) {
+  if (!split) return tile_ctas<Op>(tl, tl.n_tiles);
+  return tile_ctas<Op>(tl, tl.n_halo_tiles) + tile_ctas<Op>(tl, tl.n_tiles - tl.n_halo_tiles);
+}
 
 template <int D, class Op>
 inline void run_tile_pass(const char* name, const LaunchCfg& c, const DevTiling& tl, const typename Op::Args& a) {
@@ -448,9 +457,15 @@ inline void run_tile_pass(const char* name, const LaunchCfg& c, const DevTiling&
     }
     attr_set[c.device & 63] = smem;
   }
+  const bool split = c.part != 0;
   if (c.phase != 2) {
-    kern<<<tile_grid<Op>(tl), Op::BLOCK, smem, c.stream>>>(tl, a);
-    note_launch(name, c.stream);
+    int t0 = 0, t1 = tl.n_tiles, red_off = 0;
+    if (c.part == 1) t1 = tl.n_halo_tiles;
+    if (c.part == 2) { t0 = tl.n_halo_tiles; red_off = tile_ctas<Op>(tl, tl.n_halo_tiles); }
+    if (t1 > t0) {
+      kern<<<tile_ctas<Op>(tl, t1 - t0), Op::BLOCK, smem, c.stream>>>(tl, a, t0, t1, red_off);
+      note_launch(name, c.stream);
+    }
   }
   if (c.ev_mid) cudaEventRecord(c.ev_mid, c.stream);
   if (tl.n_boundary > 0 && c.phase != 1) {
@@ -467,9 +482,9 @@ inline void run_tile_pass(const char* name, const LaunchCfg& c, const DevTiling&
     at[0].val.programmaticStreamSerializationAllowed = 1;
     lc.attrs = at;
     lc.numAttrs = 1;
-    cudaLaunchKernelEx(&lc, k_boundary<D, Op>, tl, a, tile_grid<Op>(tl));
+    cudaLaunchKernelEx(&lc, k_boundary<D, Op>, tl, a, tile_grid<Op>(tl, split));
 #else
-    k_boundary<D, Op><<<nb, kBoundaryBlock, 0, c.stream>>>(tl, a, tile_grid<Op>(tl));
+    k_boundary<D, Op><<<nb, kBoundaryBlock, 0, c.stream>>>(tl, a, tile_grid<Op>(tl, split));
 #endif
     note_launch(name, c.stream);
   }

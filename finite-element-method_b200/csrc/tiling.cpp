@@ -104,7 +104,10 @@ std::string build_tiling(int dim, int n_vert, int n_elem, const float* verts,
     // Tile count: ~88 % fill, so that cuts can snap to coordinate gaps (planar tile faces).  When the
     // tile kernels run only a few waves of CTAs (wave = CTAs resident on the device; multi-GPU slabs),
     // round the count up to whole waves of equal tiles: a 6.05-wave launch costs 7 tile times otherwise.
-    const int Tf = tile_elems - tile_elems / 8;
+#ifndef FEMB_TILE_SLACK
+#define FEMB_TILE_SLACK 64
+#endif
+    const int Tf = tile_elems - tile_elems / FEMB_TILE_SLACK;
     int k0 = std::max(1, (int)(((int64_t)n_elem + Tf - 1) / Tf));
     if (wave > 0 && k0 >= wave && k0 < 64 * wave) k0 = (k0 + wave - 1) / wave * wave;
     k0 = std::min(k0, n_elem);
@@ -119,6 +122,37 @@ std::string build_tiling(int dim, int n_vert, int n_elem, const float* verts,
   tbeg.push_back(n_elem);
   const int nt = (int)tbeg.size() - 1;
   t.n_tiles = nt;
+  // 2b. multi-GPU: tiles that touch a halo vertex go FIRST (stable), so that the tile kernel can be
+  //     launched in two parts and the halo exchange overlaps the interior part.
+  t.n_halo_tiles = 0;
+  if (n_halo > 0) {
+    std::vector<char> is_halo(n_vert, 0);
+    for (int k = 0; k < n_halo; ++k) {
+      if (halo_verts[k] < 0 || halo_verts[k] >= n_vert) return "halo vertex out of range";
+      is_halo[halo_verts[k]] = 1;
+    }
+    std::vector<char> th(nt, 0);
+#pragma omp parallel for schedule(dynamic, 8)
+    for (int ti = 0; ti < nt; ++ti) {
+      char f = 0;
+      for (int i = tbeg[ti]; i < tbeg[ti + 1] && !f; ++i)
+        for (int c = 0; c < nc; ++c) f |= is_halo[elems[(int64_t)order[i] * nc + c]];
+      th[ti] = f;
+    }
+    std::vector<int32_t> order2;
+    order2.reserve(n_elem);
+    std::vector<int> tbeg2;
+    for (int pass = 1; pass >= 0; --pass)
+      for (int ti = 0; ti < nt; ++ti)
+        if (th[ti] == pass) {
+          tbeg2.push_back((int)order2.size());
+          order2.insert(order2.end(), order.begin() + tbeg[ti], order.begin() + tbeg[ti + 1]);
+          t.n_halo_tiles += pass;
+        }
+    tbeg2.push_back(n_elem);
+    order.swap(order2);
+    tbeg.swap(tbeg2);
+  }
   t.tiles.assign(nt, TileDesc{});
 
   // 3. per tile: sorted element list, unique vertices, tile-incidence count per vertex

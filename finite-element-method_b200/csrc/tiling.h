@@ -63,6 +63,7 @@ struct Tiling {
   int n_vert = 0, n_elem = 0;
   int T = 0;            // requested max elements per tile
   int n_tiles = 0, n_slots = 0;
+  int n_halo_tiles = 0;   // multi-GPU: tiles [0, n_halo_tiles) touch a halo vertex
   int n_interior = 0, n_boundary = 0, n_partials = 0;
   int max_tile_elems = 0, max_lv = 0, max_rounds = 0;
   std::vector<int32_t> new_of_old, old_of_new;     // vertex renumbering
