@@ -48,6 +48,7 @@ static void assemble(femb_object* o, float dt, bool with_diag) {
 namespace {
 
 using PassFn = std::function<void(const LaunchCfg&)>;
+constexpr bool kApplyPersist = FEMB_PERSIST_APPLY != 0;   // the operator passes use the persistent tile kernel
 using SumFn = std::function<void(int, const double*, const PeerComm&)>;
 
 struct Builder {
@@ -58,14 +59,17 @@ struct Builder {
   void add(std::function<void()> f, int comm = FEMB_COMM_NONE) { L->push_back(SolveOp{std::move(f), comm}); }
 
   // one tile pass (tile kernel + boundary kernel); multi-GPU: split around the halo exchange
-  void pass(PassFn f) {
+  void pass(PassFn f, bool persistent_op = false) {
     femb_object* ob = o;
     if (!dist) {
       add([ob, f] { ob->prep_full_pass(); f(ob->cfg); });
       return;
     }
     if (ob->peer_on) {   // halo sums through peer memory, inside our own kernels: no communication point
-      add([ob, f] { ob->peer_pass(f); });
+      // (an in-line send for the persistent operator kernels was measured slower than the side stream: N=2 C4
+      //  A^T A-CG 0.372 vs 0.359 ms/iteration)
+      (void)persistent_op;
+      add([ob, f] { ob->peer_pass(f, true); });
       return;
     }
     add([ob, f] {
@@ -137,21 +141,21 @@ void build_program(femb_object* o, SolveProgram& P, float dt, int method, int pr
     // ---- conjugate gradient, implicit.py:311-386
     const float4* rhs = iv.b;
     if (preconditioned == 1) {                         // ATb = A^T b, ATA = A^T A (289-299)
-      pro.pass(apply(1, iv.b, iv.atb, AP_PLAIN, nullptr, nullptr, nullptr));
-      pro.pass(apply(0, iv.b, iv.tmp, AP_PLAIN, nullptr, nullptr, nullptr));
-      pro.pass(apply(1, iv.tmp, iv.q, AP_PLAIN, nullptr, nullptr, nullptr));
+      pro.pass(apply(1, iv.b, iv.atb, AP_PLAIN, nullptr, nullptr, nullptr), kApplyPersist);
+      pro.pass(apply(0, iv.b, iv.tmp, AP_PLAIN, nullptr, nullptr, nullptr), kApplyPersist);
+      pro.pass(apply(1, iv.tmp, iv.q, AP_PLAIN, nullptr, nullptr, nullptr), kApplyPersist);
       rhs = iv.atb;
     } else {
-      pro.pass(apply(0, iv.b, iv.q, AP_PLAIN, nullptr, nullptr, nullptr));
+      pro.pass(apply(0, iv.b, iv.q, AP_PLAIN, nullptr, nullptr, nullptr), kApplyPersist);
     }
     pro.add([=] { launch_cg_init(o->cfg, nv, iv, rhs, iv.q, o->d_red, mask); });   // x = b, r = rhs - op(x), d = r
     pro.gsum(vred, [=](int n, const double* red, const PeerComm& pc) { launch_cg_delta0(o->cfg, n, red, sc, ktol, max_iter, pc); });
 
     if (preconditioned == 1) {
-      it.pass(apply(0, iv.d, iv.tmp, AP_PLAIN, nullptr, nullptr, sc));
-      it.pass(apply(1, iv.tmp, iv.q, AP_DOT, iv.d, nullptr, sc));
+      it.pass(apply(0, iv.d, iv.tmp, AP_PLAIN, nullptr, nullptr, sc), kApplyPersist);
+      it.pass(apply(1, iv.tmp, iv.q, AP_DOT, iv.d, nullptr, sc), kApplyPersist);
     } else {
-      it.pass(apply(0, iv.d, iv.q, AP_DOT, iv.d, nullptr, sc));
+      it.pass(apply(0, iv.d, iv.q, AP_DOT, iv.d, nullptr, sc), kApplyPersist);
     }
     it.gsum(ared, [=](int n, const double* red, const PeerComm& pc) { launch_cg_alpha(o->cfg, n, red, sc, pc); });
     it.add([=] { launch_cg_update_xr(o->cfg, nv, iv, o->d_red, sc, mask); });
@@ -161,7 +165,7 @@ void build_program(femb_object* o, SolveProgram& P, float dt, int method, int pr
     // ---- the reference's damped "Jacobi" (227-262, 391-404) as a true parallel Jacobi
     pro.pass([o, dim, dt](const LaunchCfg& c) { launch_implicit_diag(dim, c, o->dtl, o->h, o->vs, dt, o->iv); });
     pro.add([=] { launch_scale_xyz(o->cfg, nv, iv.b, iv.x, 0.5f); });               // x0 = 0.5 b (231-232)
-    it.pass(apply(0, iv.x, iv.tmp, AP_RESID, iv.b, iv.r, sc));
+    it.pass(apply(0, iv.x, iv.tmp, AP_RESID, iv.b, iv.r, sc), kApplyPersist);
     it.gsum(ared, [=](int n, const double* red, const PeerComm& pc) { launch_jacobi_decide(o->cfg, n, red, sc, tol, max_iter, fixed, pc); });
     it.add([=] { launch_jacobi_update(o->cfg, nv, iv, sc); });
   }

@@ -125,13 +125,23 @@ struct femb_object {
   bool pass_split() const { return peer_on && side && dtl.n_halo_tiles > 0 && dtl.n_halo_tiles < dtl.n_tiles; }
   // One tile pass of a slab rank over peer memory.  f(cfg) launches the pass's kernels for the phase / part
   // in cfg:   halo tiles | send (side stream) || other tiles | wait for the neighbours | boundary kernel
+  // side_send: run the send on the side stream (right for one-CTA-per-tile kernels, whose CTAs keep
+  // retiring and leave it room); persistent tile kernels hold every SM slot until they end, so for them the
+  // send is issued in-line between the two parts -- its NVLink flight still overlaps the second part.
   template <class F>
-  void peer_pass(F f) {
+  void peer_pass(F f, bool side_send = true) {
     using namespace femb;
     LaunchCfg c1 = cfg, c2 = cfg;
     c1.phase = 1;
     c2.phase = 2;
-    if (pass_split()) {
+    if (pass_split() && !side_send) {
+      c1.part = 1;
+      f(c1);
+      launch_halo_send(c1, dtl, peer, halo, vs.partial, vs.pos, 0);
+      c1.part = 2;
+      f(c1);
+      c2.part = 1;
+    } else if (pass_split()) {
       c1.part = 1;
       f(c1);
       FEMB_CUDA(cudaEventRecord(ev_fork, stream));
