@@ -258,6 +258,14 @@ def run_ours(args):
                 "unit": "GB/s", "frac": round(ach / peak, 4), "traffic": None, "peak_source": peak_src,
                 "bytes_per_launch": bts}
 
+    # measured DRAM traffic of the dominant kernel (one ncu --set full capture, committed under profiles/)
+    tpath = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    if os.path.exists(tpath) and world == 1:
+        tr = json.load(open(tpath)).get(args.workload)
+        if tr:
+            roof["traffic"] = tr["traffic_bytes"]
+            roof["traffic_source"] = tr["source"]
+
     # ---- e2e: the same step through the reference-shaped Python API with pinned host buffers
     e2e = measure_e2e(args, h, c, kind, w, pos0, vel0, ne_global, world, torch, barrier, halo)
 
@@ -386,12 +394,16 @@ def cpu_run(kind, w, cells, steps):
     return it / t, t
 
 
-def cpu_baseline(kind, w, sample_cells):
+def cpu_baseline(kind, w, sample_cells, budget_s=12.0):
+    """The reference algorithm (oracle C/OpenMP port) on all host cores, on a bounded sample of the workload:
+    a short calibration run sizes the step count to about `budget_s` seconds of CPU work."""
     from oracle import cref
 
     cells = tuple(min(a, b) for a, b in zip(w["cells"], sample_cells))
     ne = cells[0] * cells[1] * cells[2] * 6
-    value, t = cpu_run(kind, w, cells, 5 if kind == "explicit" else 10)
+    _, t_cal = cpu_run(kind, w, cells, 3)
+    n = int(max(5, min(2000, budget_s / max(t_cal / 3, 1e-6))))
+    value, t = cpu_run(kind, w, cells, n)
     scale = 1.0 if kind == "explicit" else ne / (w["cells"][0] * w["cells"][1] * w["cells"][2] * 6)
     return {"value": value * scale, "unit": "tet-updates/s" if kind == "explicit" else "iterations/s (scaled to the full mesh)",
             "cores": cref.threads(), "kind": "port",
@@ -409,11 +421,17 @@ def run_reference(args):
 
     w = WORKLOADS[args.workload]
     kind = w["kind"]
-    cells = tuple(min(a, b) for a, b in zip(w["cells"], args.cpu_cells))
-    ne = cells[0] * cells[1] * cells[2] * 6
     full = w["cells"][0] * w["cells"][1] * w["cells"][2] * 6
-    cpu_run(kind, w, cells, max(1, args.warmup // 4))
-    steps = max(1, min(args.steps, 20))
+    # exactly --steps steps; the sample (a sub-box of the workload) is shrunk until they fit ~90 s of CPU work
+    cells = tuple(min(a, b) for a, b in zip(w["cells"], args.cpu_cells))
+    while True:
+        _, t_cal = cpu_run(kind, w, cells, 2)
+        if t_cal / 2 * (args.steps + args.warmup) <= 90.0 or max(cells) <= 16:
+            break
+        cells = tuple(max(16, c * 3 // 4) for c in cells)
+    ne = cells[0] * cells[1] * cells[2] * 6
+    cpu_run(kind, w, cells, max(1, args.warmup))
+    steps = max(1, args.steps)
     value, t = cpu_run(kind, w, cells, steps)
     if kind != "explicit":
         value *= ne / full
@@ -421,7 +439,7 @@ def run_reference(args):
     print(json.dumps({
         "impl": "reference", "metric": "tet_element_updates_per_sec" if kind == "explicit" else "solver_iterations_per_sec",
         "value": value, "unit": "tet-updates/s" if kind == "explicit" else "iterations/s",
-        "n_gpus": args.gpus, "steps": steps, "warmup": max(1, args.warmup // 4), "ms_per_step": t / steps * 1e3,
+        "n_gpus": args.gpus, "steps": steps, "warmup": max(1, args.warmup), "ms_per_step": t / steps * 1e3,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic Kuhn tet box (bounded sample of the workload)",
         "config": {"workload": args.workload, "cells": list(w["cells"]), "n_tets": full, "sample": sample},
