@@ -234,6 +234,35 @@ int femb_implicit_apply(femb_object* o, float dt, int32_t transpose, const float
   FEMB_CATCH
 }
 
+int femb_implicit_apply_timed(femb_object* o, float dt, int32_t transpose, int32_t n, float* tile_ms, float* boundary_ms) {
+  FEMB_TRY
+  if (!o || n <= 0 || !tile_ms || !boundary_ms) throw ArgError("femb_implicit_apply_timed: bad argument");
+  if (!o->implicit) throw StateError("object was created without implicit buffers");
+  FEMB_CUDA(cudaSetDevice(o->device));
+  o->prep_full_pass();
+  std::vector<cudaEvent_t> ev((size_t)n * 3);
+  for (auto& e : ev) FEMB_CUDA(cudaEventCreate(&e));
+  LaunchCfg cfg = o->cfg;
+  for (int s = 0; s < n; ++s) {      // q = A d (or A^T d) on the vectors of the last solve: same traffic as in the solve
+    FEMB_CUDA(cudaEventRecord(ev[3 * s], o->stream));
+    cfg.ev_mid = ev[3 * s + 1];
+    launch_apply(o->dim, cfg, o->dtl, o->h, o->vs, dt, transpose, o->iv.d, o->iv.q, AP_DOT, o->iv.d, nullptr, o->d_red,
+                 nullptr);
+    FEMB_CUDA(cudaEventRecord(ev[3 * s + 2], o->stream));
+  }
+  FEMB_CUDA(cudaStreamSynchronize(o->stream));
+  double t = 0.0, b = 0.0;
+  for (int s = 0; s < n; ++s) {
+    float ms = 0.f;
+    FEMB_CUDA(cudaEventElapsedTime(&ms, ev[3 * s], ev[3 * s + 1])); t += ms;
+    FEMB_CUDA(cudaEventElapsedTime(&ms, ev[3 * s + 1], ev[3 * s + 2])); b += ms;
+  }
+  for (auto& e : ev) cudaEventDestroy(e);
+  *tile_ms = (float)t;
+  *boundary_ms = (float)b;
+  FEMB_CATCH
+}
+
 int femb_implicit_solve(femb_object* o, float dt, int32_t method, int32_t preconditioned, int32_t max_iter,
                         float tol, int32_t* iters_out, float* resid_out) {
   FEMB_TRY

@@ -186,20 +186,22 @@ struct OpExplicit {
     cofactor<D>(F, C);                                                    // F^-T = C / det
     const float J = det<D>(F);
     const float log_j = logf(J);                                          // explicit.py:24 (no clamp)
-    const float inv_j = 1.f / J;
     const float V = e0.z;
-    // P = mu F - mu F^-T + lambda log(J) F^-T                            (explicit.py:25)
-    const float cf = (a.mat.lambda * log_j - a.mat.mu) * inv_j;
+    // V * P = V * (mu F - mu F^-T + lambda log(J) F^-T), F^-T = C / J   (explicit.py:25, 28): the volume is
+    // folded into the two scalar coefficients (18 instead of 27 multiplies); the division by J is the
+    // 2-ulp fast division -- far inside the 1e-5 force tolerance, and J <= 0 gives NaN/inf either way
+    const float muV = a.mat.mu * V;
+    const float cfV = __fdividef((a.mat.lambda * log_j - a.mat.mu) * V, J);
     Mat<D> P, G;
 #pragma unroll
     for (int i = 0; i < D; ++i)
 #pragma unroll
-      for (int j = 0; j < D; ++j) P.m[i][j] = a.mat.mu * F.m[i][j] + cf * C.m[i][j];
+      for (int j = 0; j < D; ++j) P.m[i][j] = muV * F.m[i][j] + cfV * C.m[i][j];
     matmul_nt<D>(P, R, G);                                                // @ R_inv^T
 #pragma unroll
     for (int j = 0; j < D; ++j)
 #pragma unroll
-      for (int i = 0; i < D; ++i) out[j * D + i] = G.m[i][j] * V;        // force *= V (28)
+      for (int i = 0; i < D; ++i) out[j * D + i] = G.m[i][j];
     if (MODE == EX_ENERGY) {
       // explicit_auto_diff.py:25-30
       float tr = 0.f;

@@ -103,10 +103,10 @@ __device__ __forceinline__ void stage_element(float* stage, int e, const float (
   if constexpr (Op::GATHER == G_STAR) {   // share of corner 0: f0 = -(sum of columns)   (explicit.py:42-49)
 #pragma unroll
     for (int i = 0; i < D; ++i) {
-      float c = out[i];
+      float c = -out[i];                 // -(a + b + c) as (-a - b) - c: the negation rides on the operands
 #pragma unroll
-      for (int j = 1; j < D; ++j) c += out[j * D + i];
-      s[(D * D + i) * S] = -c;
+      for (int j = 1; j < D; ++j) c -= out[j * D + i];
+      s[(D * D + i) * S] = c;
     }
   }
 }

@@ -28,7 +28,7 @@ EXPORTS = [
     "femb_halo_bind", "femb_halo_mass", "femb_explicit_step_phase",
     "femb_comm_bytes", "femb_peer_bind", "femb_peer_mass", "femb_reduce_bind", "femb_implicit_solve_begin", "femb_implicit_solve_advance", "femb_implicit_solve_poll",
     "femb_implicit_solve_finish",
-    "femb_advect_implicit", "femb_implicit_assemble", "femb_implicit_apply", "femb_get", "femb_set",
+    "femb_advect_implicit", "femb_implicit_assemble", "femb_implicit_apply", "femb_implicit_apply_timed", "femb_get", "femb_set",
     "femb_get_energy", "femb_sync", "femb_last_error", "femb_launch_count", "femb_version",
     "femb_tiling_build", "femb_tiling_destroy", "femb_tiling_info", "femb_tiling_get",
 ]
@@ -107,6 +107,7 @@ def lib():
         "femb_advect_implicit": (C.c_int, [vp, f32, fp]),
         "femb_implicit_assemble": (C.c_int, [vp, f32]),
         "femb_implicit_apply": (C.c_int, [vp, f32, i32, fp, fp]),
+        "femb_implicit_apply_timed": (C.c_int, [vp, f32, i32, i32, fp, fp]),
         "femb_get": (C.c_int, [vp, i32, vp, C.c_size_t]),
         "femb_set": (C.c_int, [vp, i32, vp, C.c_size_t]),
         "femb_get_energy": (C.c_int, [vp, fp]),
@@ -327,6 +328,11 @@ class Handle:
         out = np.empty_like(a)
         check(lib().femb_implicit_apply(self._h, float(dt), int(bool(transpose)), _fptr(a), _fptr(out)))
         return out
+
+    def implicit_apply_timed(self, dt, transpose, n):
+        t, b = C.c_float(), C.c_float()
+        check(lib().femb_implicit_apply_timed(self._h, float(dt), int(bool(transpose)), int(n), C.byref(t), C.byref(b)))
+        return t.value, b.value
 
     def sync(self):
         check(lib().femb_sync(self._h))

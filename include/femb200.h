@@ -184,6 +184,12 @@ int femb_implicit_assemble(femb_object *obj, float dt);
 /* out = A in (transpose==0) or A^T in (transpose!=0); host vectors [n_vert*dim] */
 int femb_implicit_apply(femb_object *obj, float dt, int32_t transpose, const float *in, float *out);
 
+/* n operator passes q = A d (transpose != 0: A^T d) on the vectors of the last solve, launched one by one
+ * with CUDA events around each kernel: summed device time (ms) of the tile kernel and of the boundary
+ * kernel.  Measurement aid for bench.py's per-kernel roofline; synchronises. */
+int femb_implicit_apply_timed(femb_object *obj, float dt, int32_t transpose, int32_t n, float *tile_ms,
+                              float *boundary_ms);
+
 /* ---- field access: field.to_numpy() / field.from_numpy() */
 int femb_get(femb_object *obj, int32_t field, void *host, size_t bytes);
 int femb_set(femb_object *obj, int32_t field, const void *host, size_t bytes);
