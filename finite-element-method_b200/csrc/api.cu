@@ -215,6 +215,7 @@ static void fill_info(const Tiling& t, femb_info* i) {
   i->smem_bytes = tile_smem_bytes(t);
   i->block_threads = kBlock;
   i->stage_stride = kStride;
+  i->n_halo_tiles = t.n_halo_tiles;
 }
 
 int femb_object_info(const femb_object* o, femb_info* out) {
@@ -576,6 +577,19 @@ int femb_tiling_build(int32_t dim, int32_t n_vert, int32_t n_elem, const float* 
   *out = nullptr;
   femb_tiling* h = new femb_tiling();
   const std::string err = build_tiling(dim, n_vert, n_elem, verts, elems, tile_elems, h->t);
+  if (!err.empty()) { delete h; throw ArgError(err); }
+  *out = h;
+  FEMB_CATCH
+}
+
+int femb_tiling_build_ex(int32_t dim, int32_t n_vert, int32_t n_elem, const float* verts, const int32_t* elems,
+                         int32_t tile_elems, int32_t n_halo, const int32_t* halo_verts, int32_t wave,
+                         femb_tiling** out) {
+  FEMB_TRY
+  if (!out) throw ArgError("NULL out");
+  *out = nullptr;
+  femb_tiling* h = new femb_tiling();
+  const std::string err = build_tiling(dim, n_vert, n_elem, verts, elems, tile_elems, h->t, n_halo, halo_verts, wave);
   if (!err.empty()) { delete h; throw ArgError(err); }
   *out = h;
   FEMB_CATCH

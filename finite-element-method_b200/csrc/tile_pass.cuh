@@ -38,9 +38,12 @@ enum GatherMode {
 // as soon as every tile CTA has started; the boundary kernel waits (grid_dependency_wait) for their
 // completion before it touches the partial sums.
 __device__ __forceinline__ void grid_launch_dependents() {
-#if FEMB_PDL
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-#endif
+}
+// end of a tile kernel: a kernel launched as programmatic dependent (second part of a split pass) may not
+// retire before the kernel it overlapped; no-op otherwise
+__device__ __forceinline__ void grid_dependency_wait_always() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 __device__ __forceinline__ void grid_dependency_wait() {
 #if FEMB_PDL
@@ -288,6 +291,7 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile_persistent(Dev
     const float r = block_sum(red, s_warp);
     if (tid == 0) Op::red_buf(a)[red_off + blockIdx.x] = (double)r;
   }
+  grid_dependency_wait_always();
 }
 
 // One CTA per tile.
@@ -382,7 +386,9 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile(DevTiling tl, 
     const float r = block_sum(red, s_warp);
     if (threadIdx.x == 0) Op::red_buf(a)[red_off + blockIdx.x] = (double)r;
   }
+  grid_dependency_wait_always();
 }
+
 constexpr int kBoundaryBlock = 256;
 
 template <int D, class Op>
@@ -462,7 +468,23 @@ inline void run_tile_pass(const char* name, const LaunchCfg& c, const DevTiling&
     int t0 = 0, t1 = tl.n_tiles, red_off = 0;
     if (c.part == 1) t1 = tl.n_halo_tiles;
     if (c.part == 2) { t0 = tl.n_halo_tiles; red_off = tile_ctas<Op>(tl, tl.n_halo_tiles); }
-    if (t1 > t0) {
+    if (t1 > t0 && c.part == 2) {
+      // second part of a split pass: independent of the first part (other tiles, other partial slots), so
+      // it is launched as a programmatic dependent -- its CTAs fill the SMs while the first part's last
+      // wave drains instead of waiting for it (no second tail)
+      cudaLaunchConfig_t lc = {};
+      lc.gridDim = dim3((unsigned)tile_ctas<Op>(tl, t1 - t0));
+      lc.blockDim = dim3(Op::BLOCK);
+      lc.dynamicSmemBytes = (size_t)smem;
+      lc.stream = c.stream;
+      cudaLaunchAttribute at[1];
+      at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      at[0].val.programmaticStreamSerializationAllowed = 1;
+      lc.attrs = at;
+      lc.numAttrs = 1;
+      cudaLaunchKernelEx(&lc, kern, tl, a, t0, t1, red_off);
+      note_launch(name, c.stream);
+    } else if (t1 > t0) {
       kern<<<tile_ctas<Op>(tl, t1 - t0), Op::BLOCK, smem, c.stream>>>(tl, a, t0, t1, red_off);
       note_launch(name, c.stream);
     }

@@ -111,9 +111,14 @@ std::string build_tiling(int dim, int n_vert, int n_elem, const float* verts,
     int k0 = std::max(1, (int)(((int64_t)n_elem + Tf - 1) / Tf));
     if (wave > 0 && k0 >= wave && k0 < 64 * wave) k0 = (k0 + wave - 1) / wave * wave;
     k0 = std::min(k0, n_elem);
+    auto rcb = [&](int k) {
+      std::iota(order.begin(), order.end(), 0);
+      std::fill(is_start.begin(), is_start.end(), 0);
 #pragma omp parallel
 #pragma omp single
-    r.run(0, n_elem, k0);
+      r.run(0, n_elem, k);
+    };
+    rcb(k0);
   }
   for (int a = 0; a < dim; ++a) std::vector<float>().swap(cen[a]);
   std::vector<int> tbeg;

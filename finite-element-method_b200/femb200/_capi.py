@@ -30,7 +30,7 @@ EXPORTS = [
     "femb_implicit_solve_finish",
     "femb_advect_implicit", "femb_implicit_assemble", "femb_implicit_apply", "femb_implicit_apply_timed", "femb_get", "femb_set",
     "femb_get_energy", "femb_sync", "femb_last_error", "femb_launch_count", "femb_version",
-    "femb_tiling_build", "femb_tiling_destroy", "femb_tiling_info", "femb_tiling_get",
+    "femb_tiling_build", "femb_tiling_build_ex", "femb_tiling_destroy", "femb_tiling_info", "femb_tiling_get",
 ]
 
 
@@ -55,7 +55,7 @@ class PeerDesc(C.Structure):
 class Info(C.Structure):
     _fields_ = [(n, C.c_int32) for n in (
         "dim", "n_vert", "n_elem", "n_tiles", "tile_elems", "max_tile_verts", "max_rounds",
-        "n_interior", "n_boundary", "n_partials", "smem_bytes", "block_threads", "stage_stride", "reserved0")] + [("device_bytes", C.c_int64)]
+        "n_interior", "n_boundary", "n_partials", "smem_bytes", "block_threads", "stage_stride", "n_halo_tiles")] + [("device_bytes", C.c_int64)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -116,6 +116,7 @@ def lib():
         "femb_launch_count": (C.c_uint64, []),
         "femb_version": (C.c_char_p, []),
         "femb_tiling_build": (C.c_int, [i32, i32, i32, fp, ip, i32, C.POINTER(vp)]),
+        "femb_tiling_build_ex": (C.c_int, [i32, i32, i32, fp, ip, i32, i32, ip, i32, C.POINTER(vp)]),
         "femb_tiling_destroy": (C.c_int, [vp]),
         "femb_tiling_info": (C.c_int, [vp, C.POINTER(Info)]),
         "femb_tiling_get": (C.c_int64, [vp, i32, vp, C.c_int64]),
@@ -352,13 +353,14 @@ def launch_count():
 class HostTiling:
     """Host-only view of the tile layout (no CUDA calls) for tests and tools."""
 
-    def __init__(self, verts, elems, tile_elems):
+    def __init__(self, verts, elems, tile_elems, halo_verts=None, wave=0):
         verts = np.ascontiguousarray(verts, dtype=np.float32)
         elems = np.ascontiguousarray(elems, dtype=np.int32)
+        halo = np.ascontiguousarray(halo_verts if halo_verts is not None else [], dtype=np.int32)
         self.dim = verts.shape[1]
         self._h = C.c_void_p()
-        check(lib().femb_tiling_build(self.dim, verts.shape[0], elems.shape[0], _fptr(verts), _iptr(elems),
-                                      int(tile_elems), C.byref(self._h)))
+        check(lib().femb_tiling_build_ex(self.dim, verts.shape[0], elems.shape[0], _fptr(verts), _iptr(elems),
+                                         int(tile_elems), int(halo.size), _iptr(halo), int(wave), C.byref(self._h)))
         i = Info()
         check(lib().femb_tiling_info(self._h, C.byref(i)))
         self.info = i.as_dict()

@@ -86,7 +86,8 @@ typedef struct femb_info {
   int32_t n_tiles, tile_elems, max_tile_verts, max_rounds;
   int32_t n_interior, n_boundary, n_partials;
   int32_t smem_bytes, block_threads;
-  int32_t stage_stride, reserved0; /* compile-time tile capacity == staging-plane stride (JDS entry encoding) */
+  int32_t stage_stride;  /* compile-time tile capacity == staging-plane stride (JDS entry encoding) */
+  int32_t n_halo_tiles;  /* multi-GPU: tiles [0, n_halo_tiles) touch a shared vertex and are launched first */
   int64_t device_bytes; /* total device memory owned by the object */
 } femb_info;
 
@@ -206,6 +207,10 @@ const char *femb_version(void);
 /* ---- host-only tiling (no CUDA calls): used by tests to check the layout invariants */
 int femb_tiling_build(int32_t dim, int32_t n_vert, int32_t n_elem, const float *verts,
                       const int32_t *elems, int32_t tile_elems, femb_tiling **out);
+/* same with shared (halo) vertices and the device's wave size (CTAs resident at once; 0 = do not round) */
+int femb_tiling_build_ex(int32_t dim, int32_t n_vert, int32_t n_elem, const float *verts, const int32_t *elems,
+                         int32_t tile_elems, int32_t n_halo, const int32_t *halo_verts, int32_t wave,
+                         femb_tiling **out);
 int femb_tiling_destroy(femb_tiling *t);
 int femb_tiling_info(const femb_tiling *t, femb_info *out);
 /* what: 0 new_of_old[n_vert], 1 slot_of_elem[n_elem], 2 tile descriptors [n_tiles*12],
