@@ -98,6 +98,7 @@ int femb_object_create(const femb_desc* d, femb_object** out) {
       T /= 2;  // irregular mesh with very many vertices per tile: shrink the tiles
     }
     const Tiling& t = o->til;
+    if (dim == 2) o->elems2d.assign(d->elems, d->elems + (size_t)d->n_elem * 3);
 
     FEMB_CUDA(cudaStreamCreateWithFlags(&o->stream, cudaStreamNonBlocking));
     o->own_stream = true;
@@ -276,6 +277,42 @@ int femb_energy_grad(femb_object* o, float* U_out) {
   const int nbb = (o->dtl.n_boundary + 255) / 256;
   launch_reduce_final(o->cfg, energy_tile_grid(o->dtl) + nbb, o->d_red, o->d_U);
   if (U_out) return femb_get_energy(o, U_out);
+  FEMB_CATCH
+}
+
+int femb_render(femb_object* o, const femb_view* v, const int32_t* prims, int32_t n_prims, uint8_t* rgb_out) {
+  FEMB_TRY
+  if (!o || !v || !rgb_out) throw ArgError("femb_render: NULL argument");
+  if (v->width <= 0 || v->height <= 0 || (int64_t)v->width * v->height > (1 << 26)) throw ArgError("femb_render: bad image size");
+  if (n_prims < 0 || (n_prims > 0 && !prims)) throw ArgError("femb_render: bad primitive list");
+  FEMB_CUDA(cudaSetDevice(o->device));
+  if (o->dim == 2 && !prims) { prims = o->elems2d.data(); n_prims = o->n_elem; }
+  if (o->dim == 2 && n_prims != o->n_elem) throw ArgError("femb_render: 2D primitives are the object's elements (phi is per element)");
+  if (o->prims_version != v->prims_version || o->n_prims != n_prims) {
+    for (int64_t i = 0; i < (int64_t)n_prims * 3; ++i)
+      if (prims[i] < 0 || prims[i] >= o->n_vert) throw ArgError("femb_render: vertex index out of range");
+    FEMB_CUDA(cudaStreamSynchronize(o->stream));
+    o->d_prims = n_prims ? o->alloc<int32_t>((size_t)n_prims * 3, false) : nullptr;
+    if (n_prims)
+      FEMB_CUDA(cudaMemcpyAsync(o->d_prims, prims, (size_t)n_prims * 3 * sizeof(int32_t), cudaMemcpyHostToDevice, o->stream));
+    FEMB_CUDA(cudaStreamSynchronize(o->stream));
+    o->n_prims = n_prims;
+    o->prims_version = v->prims_version;
+  }
+  const int npx = v->width * v->height;
+  if (npx > o->fb_pixels) {
+    o->d_fb = o->alloc<unsigned long long>((size_t)npx, false);
+    o->d_rgb = o->alloc<uint8_t>((size_t)npx * 3, false);
+    o->fb_pixels = npx;
+  }
+  if (o->dim == 2)
+    launch_render2d(o->cfg, o->n_prims, o->d_prims, o->d_new_of_old, o->d_slot_of_elem, o->vs.pos, o->d_phi, o->n_vert,
+                    o->d_blocks, o->n_blocks, o->d_fb, o->d_rgb, v->width, v->height);
+  else
+    launch_render3d(o->cfg, v->eye, v->lookat, v->up, v->fov_deg > 0.f ? v->fov_deg : 45.f, o->n_prims, o->d_prims,
+                    o->d_new_of_old, o->vs.pos, o->d_fb, o->d_rgb, v->width, v->height);
+  FEMB_CUDA(cudaMemcpyAsync(rgb_out, o->d_rgb, (size_t)npx * 3, cudaMemcpyDeviceToHost, o->stream));
+  FEMB_CUDA(cudaStreamSynchronize(o->stream));
   FEMB_CATCH
 }
 

@@ -152,6 +152,14 @@ void launch_unpack_vertex(const LaunchCfg& c, int dim, int n_vert, const int32_t
 void launch_pack_elem(const LaunchCfg& c, int dim, int n_elem, const int32_t* slot_of_elem, Planes e, Planes h,
                       const float* phi, int what, float* dst);
 
+// headless rasteriser (kernels_render.cu): what render/render.py:64-106 draws, into a device frame buffer
+void launch_render2d(const LaunchCfg& c, int n_elem, const int32_t* elems, const int32_t* new_of_old,
+                     const int32_t* slot_of_elem, const float4* pos, const float* phi, int n_vert, const float4* blocks,
+                     int n_blocks, unsigned long long* fb, uint8_t* rgb, int W, int H);
+void launch_render3d(const LaunchCfg& c, const float* eye, const float* lookat, const float* up, float fov_deg,
+                     int n_faces, const int32_t* faces, const int32_t* new_of_old, const float4* pos,
+                     unsigned long long* fb, uint8_t* rgb, int W, int H);
+
 uint64_t launch_count();
 void note_launch(const char* what, cudaStream_t s);  // counts + checks cudaGetLastError (throws std::runtime_error)
 

@@ -107,6 +107,13 @@ struct femb_object {
       halo_dirty = false;
     }
   }
+  // headless frames (femb_render): primitives in the caller's numbering + key / RGB frame buffers
+  std::vector<int32_t> elems2d;     // dim 2: the element triangles, kept for the default primitive list
+  int32_t* d_prims = nullptr;
+  int n_prims = 0, prims_version = -1;
+  unsigned long long* d_fb = nullptr;
+  uint8_t* d_rgb = nullptr;
+  int fb_pixels = 0;
   std::vector<void*> allocs;
   int64_t device_bytes = 0;
 

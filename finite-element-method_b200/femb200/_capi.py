@@ -28,7 +28,7 @@ EXPORTS = [
     "femb_halo_bind", "femb_halo_mass", "femb_explicit_step_phase",
     "femb_comm_bytes", "femb_peer_bind", "femb_peer_mass", "femb_reduce_bind", "femb_implicit_solve_begin", "femb_implicit_solve_advance", "femb_implicit_solve_poll",
     "femb_implicit_solve_finish",
-    "femb_advect_implicit", "femb_implicit_assemble", "femb_implicit_apply", "femb_implicit_apply_timed", "femb_get", "femb_set",
+    "femb_advect_implicit", "femb_implicit_assemble", "femb_implicit_apply", "femb_implicit_apply_timed", "femb_render", "femb_get", "femb_set",
     "femb_get_energy", "femb_sync", "femb_last_error", "femb_launch_count", "femb_version",
     "femb_tiling_build", "femb_tiling_build_ex", "femb_tiling_destroy", "femb_tiling_info", "femb_tiling_get",
 ]
@@ -50,6 +50,11 @@ class PeerDesc(C.Structure):
     _fields_ = [("rank", C.c_int32), ("world", C.c_int32), ("left", C.c_int32), ("right", C.c_int32),
                 ("n_left", C.c_int32), ("left_dst_off", C.c_int32), ("right_dst_off", C.c_int32),
                 ("recv_stride", C.c_int32), ("bufs", C.POINTER(C.c_void_p))]
+
+
+class View(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("eye", C.c_float * 3), ("lookat", C.c_float * 3),
+                ("up", C.c_float * 3), ("fov_deg", C.c_float), ("prims_version", C.c_int32)]
 
 
 class Info(C.Structure):
@@ -108,6 +113,7 @@ def lib():
         "femb_implicit_assemble": (C.c_int, [vp, f32]),
         "femb_implicit_apply": (C.c_int, [vp, f32, i32, fp, fp]),
         "femb_implicit_apply_timed": (C.c_int, [vp, f32, i32, i32, fp, fp]),
+        "femb_render": (C.c_int, [vp, C.POINTER(View), ip, i32, C.POINTER(C.c_uint8)]),
         "femb_get": (C.c_int, [vp, i32, vp, C.c_size_t]),
         "femb_set": (C.c_int, [vp, i32, vp, C.c_size_t]),
         "femb_get_energy": (C.c_int, [vp, fp]),
@@ -334,6 +340,20 @@ class Handle:
         t, b = C.c_float(), C.c_float()
         check(lib().femb_implicit_apply_timed(self._h, float(dt), int(bool(transpose)), int(n), C.byref(t), C.byref(b)))
         return t.value, b.value
+
+    def render(self, width=640, height=640, prims=None, prims_version=0, eye=(-6.36, 3.49, 2.44),
+               lookat=(-5.40, 3.19, 2.43), up=(0.0, 1.0, 0.0), fov_deg=45.0):
+        """One headless frame (render/render.py:64-98) -> uint8 [height, width, 3], row 0 at the top.
+        prims: 3D surface triangles [n, 3] in the caller's vertex numbering; None in 2D (the elements)."""
+        v = View(int(width), int(height), (C.c_float * 3)(*eye), (C.c_float * 3)(*lookat), (C.c_float * 3)(*up),
+                 float(fov_deg), int(prims_version))
+        n, pp = 0, None
+        if prims is not None:
+            prims = np.ascontiguousarray(prims, np.int32).reshape(-1, 3)
+            n, pp = len(prims), prims.ctypes.data_as(C.POINTER(C.c_int32))
+        img = np.empty((int(height), int(width), 3), np.uint8)
+        check(lib().femb_render(self._h, C.byref(v), pp, n, img.ctypes.data_as(C.POINTER(C.c_uint8))))
+        return img
 
     def sync(self):
         check(lib().femb_sync(self._h))

@@ -135,7 +135,7 @@ if __name__ == '__main__':
                     soft_obj.save_obj(os.path.join(args.out, '{:06d}.obj'.format(ply_cnt)))
                 ply_cnt += 1
         if render is not None:
-            render.render(soft_objects, circle_blocks)
+            render.render(soft_objects, circle_blocks, virtual_time)
         if args.diag_every and (frame_cnt + 1) % args.diag_every == 0:
             for k, o in enumerate(soft_objects):
                 print('frame {} object {}: {}'.format(frame_cnt + 1, k, json.dumps(diagnostics(o))))

@@ -191,6 +191,22 @@ int femb_implicit_apply(femb_object *obj, float dt, int32_t transpose, const flo
 int femb_implicit_apply_timed(femb_object *obj, float dt, int32_t transpose, int32_t n, float *tile_ms,
                               float *boundary_ms);
 
+/* ---- headless frame (render/render.py: Render.render2d :64-75, render3d :86-98).  The reference draws
+ * through a Taichi GUI / GGUI (Vulkan) window, unavailable on this box; the same picture is rasterised by
+ * CUDA kernels into a device frame buffer and returned as width*height*3 RGB8 bytes, row 0 = top.
+ *   dim 2: element triangles coloured (phi+0.13, 0.13, 0.13), vertex dots (radius 2 px, 0xAAAA00), blocks
+ *          (radius r*width, 0x343434); unit square -> image, y up.  prims = NULL (the object's elements).
+ *   dim 3: the (0..5)^3 box (colour (0.99,0.68,0.28), width 2) and the surface mesh prims[n_prims*3]
+ *          (obj.indices, ORIGINAL vertex numbering) as a wireframe shaded with ambient 0.8 + the point light
+ *          at (3.5,3.5,3.5); look-at perspective camera.  prims are uploaded when prims_version changes. */
+typedef struct femb_view {
+  int32_t width, height;      /* render.py:11-12: 640 x 640 */
+  float eye[3], lookat[3], up[3];   /* render.py:37-39 */
+  float fov_deg;              /* GGUI default 45 */
+  int32_t prims_version;      /* bump to re-upload prims (a new surface) */
+} femb_view;
+int femb_render(femb_object *obj, const femb_view *view, const int32_t *prims, int32_t n_prims, uint8_t *rgb_out);
+
 /* ---- field access: field.to_numpy() / field.from_numpy() */
 int femb_get(femb_object *obj, int32_t field, void *host, size_t bytes);
 int femb_set(femb_object *obj, int32_t field, const void *host, size_t bytes);
