@@ -147,7 +147,9 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     from femb200 import _capi as c
 
-    w = WORKLOADS[args.workload]
+    w = dict(WORKLOADS[args.workload])
+    if args.x_cells:      # diagnostic only: a thinner box (e.g. the per-rank slab of a larger N); not a bench line
+        w["cells"] = (args.x_cells,) + tuple(w["cells"][1:])
     kind = w["kind"]
     mu, lam = lame(MAT["E"], MAT["nu"])
     verts, tets, center, pos0, (i0, i1) = make_state(w, rank, world)
@@ -431,7 +433,9 @@ def run_reference(args):
         return
     from oracle import cref
 
-    w = WORKLOADS[args.workload]
+    w = dict(WORKLOADS[args.workload])
+    if args.x_cells:      # diagnostic only: a thinner box (e.g. the per-rank slab of a larger N); not a bench line
+        w["cells"] = (args.x_cells,) + tuple(w["cells"][1:])
     kind = w["kind"]
     full = w["cells"][0] * w["cells"][1] * w["cells"][2] * 6
     # exactly --steps steps; the sample (a sub-box of the workload) is shrunk until they fit ~90 s of CPU work
@@ -474,6 +478,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=20)
     ap.add_argument("--cpu-cells", type=int, nargs=3, default=[96, 96, 96], help="CPU sample size in cells")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--x-cells", type=int, default=0, help="diagnostic: override the box's cell count along x")
     ap.add_argument("--comm", default=None, choices=["peer", "nccl"], help="multi-GPU transport (default: peer memory)")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -470,6 +470,22 @@ int femb_peer_bind(femb_object* o, const femb_peer_desc* d) {
   }
   o->d_allred_own = o->alloc<double>(1);
   o->d_allred = o->d_allred_own;
+  {
+    // device-resident exchange description for the kernels that send / receive themselves
+    const char* env = std::getenv("FEMB_PEER_FUSED");
+    const bool fused = !(env && env[0] == '0');
+    std::vector<int32_t> bhalo((size_t)o->dtl.n_boundary, -1);
+    for (size_t k = 0; k < o->til.halo_b.size(); ++k) bhalo[(size_t)o->til.halo_b[k]] = (int32_t)k;
+    int32_t* d_bhalo = o->alloc<int32_t>(bhalo.size(), false);
+    FEMB_CUDA(cudaMemcpyAsync(d_bhalo, bhalo.data(), bhalo.size() * sizeof(int32_t), cudaMemcpyHostToDevice, o->stream));
+    HaloDev hd{pc, o->halo.n, o->halo.b, d_bhalo};
+    HaloDev* d_hd = o->alloc<HaloDev>(1, false);
+    FEMB_CUDA(cudaMemcpyAsync(d_hd, &hd, sizeof(HaloDev), cudaMemcpyHostToDevice, o->stream));
+    FEMB_CUDA(cudaStreamSynchronize(o->stream));   // bhalo / hd are stack / local storage
+    o->d_halo_dev = fused ? d_hd : nullptr;
+    o->n_send_ctas = std::max(1, std::min(o->cfg.sms, (o->halo.n + 1023) / 1024));
+    if (const char* w = std::getenv("FEMB_PEER_FUSED_WAVES")) o->fuse_max_waves = std::atoi(w);
+  }
   FEMB_CUDA(cudaStreamSynchronize(o->stream));
   o->peer = pc;
   o->peer_on = true;

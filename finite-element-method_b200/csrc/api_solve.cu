@@ -26,8 +26,11 @@ int fail(const std::exception& ex);
   }                                  \
   return FEMB_OK;
 
+constexpr bool kApplyPersist = FEMB_PERSIST_APPLY != 0;   // the operator passes use the persistent tile kernel
+
 static int apply_red_slots(const femb_object* o) {
-  return apply_tile_grid(o->dtl, o->pass_split()) + (o->dtl.n_boundary + 255) / 256;
+  const bool fused = o->fused_pass(kApplyPersist);   // fused exchange: one CTA per tile (object.h: peer_pass)
+  return apply_tile_grid(o->dtl, o->pass_split(), !fused) + (o->dtl.n_boundary + 255) / 256;
 }
 
 static void poll(femb_object* o) {
@@ -48,7 +51,6 @@ static void assemble(femb_object* o, float dt, bool with_diag) {
 namespace {
 
 using PassFn = std::function<void(const LaunchCfg&)>;
-constexpr bool kApplyPersist = FEMB_PERSIST_APPLY != 0;   // the operator passes use the persistent tile kernel
 using SumFn = std::function<void(int, const double*, const PeerComm&)>;
 
 struct Builder {
@@ -66,10 +68,7 @@ struct Builder {
       return;
     }
     if (ob->peer_on) {   // halo sums through peer memory, inside our own kernels: no communication point
-      // (an in-line send for the persistent operator kernels was measured slower than the side stream: N=2 C4
-      //  A^T A-CG 0.372 vs 0.359 ms/iteration)
-      (void)persistent_op;
-      add([ob, f] { ob->peer_pass(f, true); });
+      add([ob, f, persistent_op] { ob->peer_pass(f, persistent_op); });
       return;
     }
     add([ob, f] {
@@ -97,6 +96,10 @@ struct Builder {
     }
     if (ob->peer_on) {
       add([ob, n_red, consume] {
+        if (ob->d_halo_dev) {   // fused: the scalar kernel sums locally, scatters, gathers and does the math
+          consume(n_red, ob->d_red, ob->peer);
+          return;
+        }
         launch_reduce_final_send(ob->cfg, n_red, ob->d_red, ob->peer);   // my partial -> every rank's slot
         consume(0, nullptr, ob->peer);                                     // gathers the slots, then the scalar math
       });

@@ -33,6 +33,64 @@ __device__ __forceinline__ float4* recv_of(char* base, const PeerComm& pc, uint3
   return reinterpret_cast<float4*>(base + pc.recv_off) + (size_t)parity * pc.recv_stride;
 }
 
+// One CTA's share of a halo send (what == 0 of k_halo_send): send[k] = sum of the local partial slots of halo
+// vertex k, stored straight into the neighbour's receive plane; the last of the n_ctas CTAs releases the flags.
+// partial is read through L2 (__ldcg): it was written by other CTAs, possibly of an overlapped kernel.
+__device__ __forceinline__ void halo_send_cta(const PeerComm& pc, int n, const int32_t* __restrict__ hb,
+                                              const int32_t* __restrict__ bptr, const float4* partial, int cta,
+                                              int n_ctas) {
+  CommState* st = pc.st;
+  const uint32_t seq = st->send_seq + 1, parity = seq & 1u;
+  float4* const lplane = pc.left ? recv_of(pc.left, pc, parity) + pc.left_dst_off : nullptr;
+  float4* const rplane = pc.right ? recv_of(pc.right, pc, parity) + pc.right_dst_off : nullptr;
+  for (int k = cta * blockDim.x + threadIdx.x; k < n; k += n_ctas * blockDim.x) {
+    const int b = hb[k];
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i = bptr[b]; i < bptr[b + 1] - 1; ++i) {
+      const float4 p = __ldcg(partial + i);
+      s.x += p.x; s.y += p.y; s.z += p.z;
+    }
+    if (k < pc.n_left) lplane[k] = s;
+    else rplane[k - pc.n_left] = s;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    const unsigned prev = atomicAdd(&st->pack_count, 1u);
+    if (prev == (unsigned)n_ctas - 1) {
+      st->pack_count = 0;
+      st->send_seq = seq;
+      __threadfence_system();
+      if (pc.left) st_release_sys(&hdr_of(pc.left)->halo_flag[1], seq);
+      if (pc.right) st_release_sys(&hdr_of(pc.right)->halo_flag[0], seq);
+    }
+  }
+}
+
+// Receive side inside a consumer kernel: every CTA waits for both neighbours' flags (begin) and the last CTA to
+// finish advances the sequence (end).  Returns the parity of the receive plane to read.
+__device__ __forceinline__ uint32_t halo_recv_begin(const PeerComm& pc, uint32_t& seq) {
+  CommState* st = pc.st;
+  seq = st->recv_seq + 1;
+  if (threadIdx.x == 0) {
+    if (pc.left) spin_until(&hdr_of(pc.self)->halo_flag[0], seq, st);
+    if (pc.right) spin_until(&hdr_of(pc.self)->halo_flag[1], seq, st);
+  }
+  __syncthreads();
+  return seq & 1u;
+}
+__device__ __forceinline__ void halo_recv_end(const PeerComm& pc, uint32_t seq) {
+  CommState* st = pc.st;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned prev = atomicAdd(&st->unpack_count, 1u);
+    if (prev == gridDim.x - 1) {
+      st->unpack_count = 0;
+      st->recv_seq = seq;
+    }
+  }
+}
+
 // this rank's partial `v` -> slot[rank] of every rank, then the flag (lanes 0..world-1 of one warp)
 __device__ __forceinline__ void allsum_scatter(const PeerComm& pc, double v, int lane) {
   const uint32_t seq = pc.st->ar_seq + 1, parity = seq & 1u;

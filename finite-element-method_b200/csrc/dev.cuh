@@ -28,6 +28,8 @@ struct DevTile {           // 16 x int32 = 64 bytes, 16-byte aligned (bulk-copie
   int32_t nx_slot_off, nx_n_elem, nx_lv_off, nx_n_lv, nx_jds_off, nx_int_base, nx_n_int;
 };
 
+struct HaloDev;   // launch.h: device-resident description of the peer-memory halo exchange
+
 // Device view of the tiling + element planes (all pointers are device memory).
 struct DevTiling {
   const DevTile* tiles;
@@ -45,6 +47,10 @@ struct DevTiling {
   int n_halo_tiles;      // multi-GPU: tiles [0, n_halo_tiles) touch a vertex shared with another rank
   const uint8_t* bskip;  // [n_boundary] multi-GPU: 1 = shared vertex counted by ANOTHER rank in global
                          // reductions (dots, norms); nullptr on single-GPU objects
+  // multi-GPU, set per launch (run_tile_pass) when the halo exchange runs INSIDE the pass's own kernels:
+  const HaloDev* hd;     // nullptr: no exchange in this launch
+  int n_send;            // tile kernel: its first n_send CTAs send the halo sums of the (finished) halo tiles
+  int fuse_recv;         // boundary kernel: wait for the neighbours and add their sums itself
 };
 
 // Shared-memory layout of k_tile (byte offsets; every region is 16-byte aligned):

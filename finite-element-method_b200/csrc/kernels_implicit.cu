@@ -271,7 +271,7 @@ void launch_apply(int dim, const LaunchCfg& c, const DevTiling& tl, Planes h, Ve
   }
 }
 
-int apply_tile_grid(const DevTiling& tl, bool split) { return tile_grid<OpApply<3, 0>>(tl, split); }
+int apply_tile_grid(const DevTiling& tl, bool split, bool persist) { return tile_grid<OpApply<3, 0>>(tl, split, persist); }
 
 int reduce_slots(const DevTiling& tl, const LaunchCfg&) {
   const int nbb = (tl.n_boundary + kBoundaryBlock - 1) / kBoundaryBlock;

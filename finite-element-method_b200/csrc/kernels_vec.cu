@@ -53,8 +53,13 @@ __device__ double final_sum(const double* red, int n) {
 // The global sum a scalar kernel consumes: single GPU -> the per-CTA partials red[0..n); multi-GPU over peer
 // memory (pc.st != nullptr) -> every rank's already-reduced partial, gathered through the comm buffers.
 // Result valid in thread 0.  In peer mode a sequence number is consumed on every call, `done` or not.
+// n > 0 in peer mode: this kernel also does the local sum and the scatter (no separate reduce kernel).
 __device__ double global_sum(const double* red, int n, const PeerComm& pc) {
   if (pc.st == nullptr) return final_sum(red, n);
+  if (n > 0) {
+    const double s = final_sum(red, n);
+    if (threadIdx.x < 32) allsum_scatter(pc, s, threadIdx.x);   // same sequence number as the gather below
+  }
   return threadIdx.x < 32 ? allsum_gather(pc, threadIdx.x) : 0.0;
 }
 

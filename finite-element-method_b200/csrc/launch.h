@@ -51,6 +51,10 @@ struct LaunchCfg {
                                  // (multi-GPU: the halo exchange of the partial sums runs between 1 and 2)
   int part = 0;                  // phase 1 only -- 0: all tiles; 1: the halo tiles [0, n_halo_tiles);
                                  // 2: the other tiles (the exchange overlaps part 2)
+  const struct HaloDev* hd = nullptr;   // peer-memory exchange fused into the pass's kernels:
+  int n_send = 0;                //   part 2: sender CTAs at the front of the tile kernel
+  int fuse_recv = 0;             //   phase 2: the boundary kernel receives
+  int no_persist = 0;            //   one CTA per tile even for Ops that default to the persistent kernel
 };
 
 struct Halo {                    // vertices shared with a neighbouring rank (slab interface planes)
@@ -79,6 +83,12 @@ struct PeerComm {                // kernel argument
   int left_dst_off, right_dst_off;   // where my planes start in the neighbours' receive arrays
   size_t recv_off, slot_off, recv_stride;
   CommState* st;
+};
+struct HaloDev {                 // device-resident: what a tile / boundary kernel needs to run the exchange itself
+  PeerComm pc;
+  int n;                         // halo vertices
+  const int32_t* hb;             // [n] boundary index of halo vertex k
+  const int32_t* bhalo;          // [n_boundary] halo index of boundary vertex b, -1: not shared
 };
 size_t comm_layout(int n_halo, size_t* recv_off, size_t* slot_off, size_t* recv_stride);
 // what: 0 partial sums, 1 lumped masses
@@ -115,7 +125,7 @@ void launch_apply(int dim, const LaunchCfg& c, const DevTiling& tl, Planes h, Ve
                   int transpose, const float4* in, float4* out, int epilogue, const float4* aux,
                   float4* resid_out, double* red, const SolveScalars* sc);
 int reduce_slots(const DevTiling& tl, const LaunchCfg& c);
-int apply_tile_grid(const DevTiling& tl, bool split = false);   // per-CTA reduction partials written by an operator pass
+int apply_tile_grid(const DevTiling& tl, bool split = false, bool persist = true);   // per-CTA reduction partials written by an operator pass
 int energy_tile_grid(const DevTiling& tl);  // ... by the energy pass  // doubles needed in a reduction buffer
 
 // CG / Jacobi vector kernels (all early-exit on sc->done)

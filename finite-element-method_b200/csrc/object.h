@@ -127,28 +127,48 @@ struct femb_object {
     if (zero) FEMB_CUDA(cudaMemsetAsync(p, 0, bytes, stream));
     return static_cast<T*>(p);
   }
+  const femb::HaloDev* d_halo_dev = nullptr;   // peer mode, fused exchange (default; FEMB_PEER_FUSED=0 disables)
+  int n_send_ctas = 0;
   cudaStream_t side = nullptr;      // peer mode: the halo send runs here, overlapping the non-halo tiles
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   bool pass_split() const { return peer_on && side && dtl.n_halo_tiles > 0 && dtl.n_halo_tiles < dtl.n_tiles; }
+  // Does a pass of this kind run with the exchange fused into its own kernels and one CTA per tile?
+  // Ops whose tile kernel is persistent keep it (plus the send kernel on the side stream) while a rank still
+  // owns many tiles per SM slot -- there the persistent kernel is worth more than the kernel boundaries the
+  // fusion removes (N=2 on C4: 0.342 vs 0.370 ms per A^T A-CG iteration); on thin slabs it is the other way
+  // round (the slab of N=8: 0.137 vs 0.123).  FEMB_PEER_FUSED_WAVES moves the threshold.
+  int fuse_max_waves = 8;
+  bool fused_pass(bool persistent_op) const {
+    if (!pass_split() || !d_halo_dev) return false;
+    return !persistent_op || (dtl.n_tiles - dtl.n_halo_tiles) <= (long long)fuse_max_waves * dtl.grid;
+  }
   // One tile pass of a slab rank over peer memory.  f(cfg) launches the pass's kernels for the phase / part
-  // in cfg:   halo tiles | send (side stream) || other tiles | wait for the neighbours | boundary kernel
-  // side_send: run the send on the side stream (right for one-CTA-per-tile kernels, whose CTAs keep
-  // retiring and leave it room); persistent tile kernels hold every SM slot until they end, so for them the
-  // send is issued in-line between the two parts -- its NVLink flight still overlaps the second part.
+  // in cfg.
+  //   fused:   halo tiles | [sender CTAs + other tiles] (programmatic dependent launch) | boundary kernel that
+  //            waits for the neighbours itself.  One stream, three kernels.
+  //   else:    halo tiles | send kernel (side stream) || other tiles | boundary kernel (receives itself when
+  //            the fused description exists, else after the receive kernel)
   template <class F>
-  void peer_pass(F f, bool side_send = true) {
+  void peer_pass(F f, bool persistent_op = false) {
     using namespace femb;
     LaunchCfg c1 = cfg, c2 = cfg;
     c1.phase = 1;
     c2.phase = 2;
-    if (pass_split() && !side_send) {
+    if (fused_pass(persistent_op)) {
+      c1.no_persist = c2.no_persist = 1;   // sender CTAs and persistent tile CTAs do not mix (run_tile_pass)
       c1.part = 1;
       f(c1);
-      launch_halo_send(c1, dtl, peer, halo, vs.partial, vs.pos, 0);
       c1.part = 2;
+      c1.hd = d_halo_dev;
+      c1.n_send = n_send_ctas;
       f(c1);
       c2.part = 1;
-    } else if (pass_split()) {
+      c2.hd = d_halo_dev;
+      c2.fuse_recv = 1;
+      f(c2);   // (the remote partial slots are not touched: halo_dirty keeps its value)
+      return;
+    }
+    if (pass_split()) {
       c1.part = 1;
       f(c1);
       FEMB_CUDA(cudaEventRecord(ev_fork, stream));
@@ -165,8 +185,13 @@ struct femb_object {
       f(c1);
       launch_halo_send(c1, dtl, peer, halo, vs.partial, vs.pos, 0);
     }
-    launch_halo_recv(c2, dtl, peer, halo, vs.partial, vs.pos, 0);
-    halo_dirty = true;
+    if (d_halo_dev) {
+      c2.hd = d_halo_dev;
+      c2.fuse_recv = 1;
+    } else {
+      launch_halo_recv(c2, dtl, peer, halo, vs.partial, vs.pos, 0);
+      halo_dirty = true;
+    }
     f(c2);
   }
   // a peer wait that timed out leaves CommState.error set: surface it (call after a stream sync)

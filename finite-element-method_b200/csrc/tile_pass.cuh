@@ -17,6 +17,7 @@
 //   slot order and finishes the vertex with the same Op::vertex.
 #pragma once
 #include "dev.cuh"
+#include "comm.cuh"
 #include "launch.h"
 #include "tma.cuh"
 
@@ -172,8 +173,15 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile_persistent(Dev
   __shared__ uint64_t s_bar[3];          // [0],[1]: descriptor + local-vertex table buffers; [2]: JDS lists
   __shared__ __align__(16) DevTile s_td[2];
   grid_launch_dependents();
+  const int n_send = tl.n_send;
+  if ((int)blockIdx.x < n_send) {   // sender CTA of a split multi-GPU pass (see run_tile_pass)
+    grid_dependency_wait_always();  // the halo tiles (the kernel this one overlaps) are complete and visible
+    halo_send_cta(tl.hd->pc, tl.hd->n, tl.hd->hb, tl.bptr, Op::partial_buf(a), blockIdx.x, n_send);
+    return;
+  }
   if (Op::early_exit(a)) return;
-  int t = t_begin + blockIdx.x;
+  const int bid = (int)blockIdx.x - n_send;
+  int t = t_begin + bid;
   if (t >= t_end) return;
   constexpr int S = kStride;
   const TileSmem lay = tile_smem_layout(tl.max_lv, tl.max_rounds, tl.nc, n_planes<D, Op>());
@@ -183,7 +191,7 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile_persistent(Dev
   uint32_t* s_rounds = reinterpret_cast<uint32_t*>(smem + lay.rounds);
   uint16_t* s_jds = reinterpret_cast<uint16_t*>(smem + lay.jds);
   float* stage = reinterpret_cast<float*>(smem + lay.stage);
-  const int B = blockDim.x, G = gridDim.x, tid = threadIdx.x;
+  const int B = blockDim.x, G = (int)gridDim.x - n_send, tid = threadIdx.x;
 
   if (tid == 0) {
     mbar_init(&s_bar[0], 1);
@@ -289,7 +297,7 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile_persistent(Dev
   }
   if (Op::REDUCE) {
     const float r = block_sum(red, s_warp);
-    if (tid == 0) Op::red_buf(a)[red_off + blockIdx.x] = (double)r;
+    if (tid == 0) Op::red_buf(a)[red_off + bid] = (double)r;
   }
   grid_dependency_wait_always();
 }
@@ -302,8 +310,15 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile(DevTiling tl, 
   __shared__ float s_warp[32];
   __shared__ uint64_t s_bar[2];   // [0]: local-vertex table landed, [1]: JDS lists landed
   grid_launch_dependents();
+  const int n_send = tl.n_send;
+  if ((int)blockIdx.x < n_send) {   // sender CTA of a split multi-GPU pass (see run_tile_pass)
+    grid_dependency_wait_always();  // the halo tiles (the kernel this one overlaps) are complete and visible
+    halo_send_cta(tl.hd->pc, tl.hd->n, tl.hd->hb, tl.bptr, Op::partial_buf(a), blockIdx.x, n_send);
+    return;
+  }
   if (Op::early_exit(a)) return;
-  const int tile = t_begin + blockIdx.x;
+  const int bid = (int)blockIdx.x - n_send;
+  const int tile = t_begin + bid;
   const DevTile td = tl.tiles[tile];
   constexpr int S = kStride;
   const TileSmem lay = tile_smem_layout(tl.max_lv, tl.max_rounds, tl.nc, n_planes<D, Op>());
@@ -384,7 +399,7 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile(DevTiling tl, 
   }
   if (Op::REDUCE) {
     const float r = block_sum(red, s_warp);
-    if (threadIdx.x == 0) Op::red_buf(a)[red_off + blockIdx.x] = (double)r;
+    if (threadIdx.x == 0) Op::red_buf(a)[red_off + bid] = (double)r;
   }
   grid_dependency_wait_always();
 }
@@ -394,12 +409,22 @@ constexpr int kBoundaryBlock = 256;
 template <int D, class Op>
 __global__ void __launch_bounds__(kBoundaryBlock) k_boundary(DevTiling tl, typename Op::Args a, int red_base) {
   __shared__ float s_warp[32];
-  if (Op::early_exit(a)) return;
+  // multi-GPU, exchange fused into this kernel: the neighbours' sums of the shared vertices are read straight
+  // from the receive plane they stored into (no unpack kernel).  The sequence bookkeeping runs even when the
+  // solver has already converged, so that all ranks keep counting the same exchanges.
+  const HaloDev* hd = tl.fuse_recv ? tl.hd : nullptr;
+  uint32_t rseq = 0, rparity = 0;
+  if (hd) rparity = halo_recv_begin(hd->pc, rseq);
+  if (Op::early_exit(a)) {
+    if (hd) halo_recv_end(hd->pc, rseq);
+    return;
+  }
   float red = 0.f;
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b < tl.n_boundary) {
     const float4* part = Op::partial_buf(a);
-    const int s0 = tl.bptr[b], s1 = tl.bptr[b + 1];
+    const int hk = hd ? hd->bhalo[b] : -1;          // >= 0: shared vertex, its last slot is the remote one
+    const int s0 = tl.bptr[b], s1 = tl.bptr[b + 1] - (hk >= 0 ? 1 : 0);
     const int gid = tl.n_interior + b;
     // the vertex operands do not depend on the partial sums: request them first
     const float4 vtx = Op::load_vertex(a, gid);
@@ -424,6 +449,12 @@ __global__ void __launch_bounds__(kBoundaryBlock) k_boundary(DevTiling tl, typen
         }
       }
     }
+    if (hk >= 0) {   // local + remote: the same two-term sum on both owners -> identical bits
+      const float4 r = __ldcv(recv_of(hd->pc.self, hd->pc, rparity) + hk);
+      acc[0] += r.x;
+      acc[1] += r.y;
+      if (D == 3) acc[D - 1] += r.z;
+    }
     Op::vertex(a, gid, vtx, pre, acc, red);
     if (Op::REDUCE && tl.bskip && tl.bskip[b]) red = 0.f;   // shared vertex owned by the neighbouring rank
   }
@@ -431,6 +462,7 @@ __global__ void __launch_bounds__(kBoundaryBlock) k_boundary(DevTiling tl, typen
     const float r = block_sum(red, s_warp);
     if (threadIdx.x == 0) Op::red_buf(a)[red_base + blockIdx.x] = (double)r;
   }
+  if (hd) halo_recv_end(hd->pc, rseq);
 }
 
 // prefetch helper shared by the Ops: `bytes` per plane starting at slot `slot`
@@ -441,20 +473,30 @@ __device__ __forceinline__ void prefetch_planes(const Planes& p, int slot, uint3
 }
 
 // CTAs the tile kernel of an Op uses for `n` tiles == per-CTA reduction partials it writes
+// persist = false forces the one-CTA-per-tile kernel (LaunchCfg::no_persist: fused multi-GPU passes)
 template <class Op>
-inline int tile_ctas(const DevTiling& tl, int n) { return Op::PERSIST ? (n < tl.grid ? n : tl.grid) : n; }
+inline int tile_ctas(const DevTiling& tl, int n, bool persist = true) {
+  return Op::PERSIST && persist ? (n < tl.grid ? n : tl.grid) : n;
+}
 // partials of a whole pass; split: the pass is launched as halo tiles + other tiles (multi-GPU overlap)
 template <class Op>
-inline int tile_grid(const DevTiling& tl, bool split = false) {
-  if (!split) return tile_ctas<Op>(tl, tl.n_tiles);
-  return tile_ctas<Op>(tl, tl.n_halo_tiles) + tile_ctas<Op>(tl, tl.n_tiles - tl.n_halo_tiles);
+inline int tile_grid(const DevTiling& tl, bool split = false, bool persist = true) {
+  if (!split) return tile_ctas<Op>(tl, tl.n_tiles, persist);
+  return tile_ctas<Op>(tl, tl.n_halo_tiles, persist) + tile_ctas<Op>(tl, tl.n_tiles - tl.n_halo_tiles, persist);
 }
 
 template <int D, class Op>
-inline void run_tile_pass(const char* name, const LaunchCfg& c, const DevTiling& tl, const typename Op::Args& a) {
+inline void run_tile_pass(const char* name, const LaunchCfg& c, const DevTiling& tl_in, const typename Op::Args& a) {
+  DevTiling tl = tl_in;          // per-launch copy: the fused halo exchange is switched on per kernel
+  tl.hd = c.hd;
+  tl.n_send = 0;
+  tl.fuse_recv = 0;
   static int attr_set[64] = {};  // per device (the attribute lives in the device's context): bytes allowed so far
   const int smem = tile_smem_layout(tl.max_lv, tl.max_rounds, tl.nc, n_planes<D, Op>()).total;
-  auto* kern = Op::PERSIST ? k_tile_persistent<D, Op> : k_tile<D, Op>;
+  // Persistent CTAs own a fixed share of the tiles, so sender CTAs that hold SM slots at the start would make
+  // the tile CTAs that wait for those slots finish late: fused multi-GPU passes use one CTA per tile.
+  const bool persist = Op::PERSIST && !c.no_persist;
+  auto* kern = persist ? k_tile_persistent<D, Op> : k_tile<D, Op>;
   if (smem > attr_set[c.device & 63]) {
     const cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) {
@@ -467,13 +509,16 @@ inline void run_tile_pass(const char* name, const LaunchCfg& c, const DevTiling&
   if (c.phase != 2) {
     int t0 = 0, t1 = tl.n_tiles, red_off = 0;
     if (c.part == 1) t1 = tl.n_halo_tiles;
-    if (c.part == 2) { t0 = tl.n_halo_tiles; red_off = tile_ctas<Op>(tl, tl.n_halo_tiles); }
+    if (c.part == 2) { t0 = tl.n_halo_tiles; red_off = tile_ctas<Op>(tl, tl.n_halo_tiles, persist); }
     if (t1 > t0 && c.part == 2) {
       // second part of a split pass: independent of the first part (other tiles, other partial slots), so
       // it is launched as a programmatic dependent -- its CTAs fill the SMs while the first part's last
       // wave drains instead of waiting for it (no second tail)
+      // With c.n_send, the first n_send CTAs are SENDERS: they wait for the first part (griddepcontrol.wait)
+      // and store the halo sums into the neighbours' memory -- no send kernel, no second stream.
+      tl.n_send = c.hd ? c.n_send : 0;
       cudaLaunchConfig_t lc = {};
-      lc.gridDim = dim3((unsigned)tile_ctas<Op>(tl, t1 - t0));
+      lc.gridDim = dim3((unsigned)(tile_ctas<Op>(tl, t1 - t0, persist) + tl.n_send));
       lc.blockDim = dim3(Op::BLOCK);
       lc.dynamicSmemBytes = (size_t)smem;
       lc.stream = c.stream;
@@ -484,13 +529,15 @@ inline void run_tile_pass(const char* name, const LaunchCfg& c, const DevTiling&
       lc.numAttrs = 1;
       cudaLaunchKernelEx(&lc, kern, tl, a, t0, t1, red_off);
       note_launch(name, c.stream);
+      tl.n_send = 0;
     } else if (t1 > t0) {
-      kern<<<tile_ctas<Op>(tl, t1 - t0), Op::BLOCK, smem, c.stream>>>(tl, a, t0, t1, red_off);
+      kern<<<tile_ctas<Op>(tl, t1 - t0, persist), Op::BLOCK, smem, c.stream>>>(tl, a, t0, t1, red_off);
       note_launch(name, c.stream);
     }
   }
   if (c.ev_mid) cudaEventRecord(c.ev_mid, c.stream);
   if (tl.n_boundary > 0 && c.phase != 1) {
+    tl.fuse_recv = c.hd ? c.fuse_recv : 0;
     const int nb = (tl.n_boundary + kBoundaryBlock - 1) / kBoundaryBlock;
 #if FEMB_PDL
     // programmatic dependent launch: the boundary kernel's CTAs are scheduled while the tile kernel drains
@@ -504,9 +551,9 @@ inline void run_tile_pass(const char* name, const LaunchCfg& c, const DevTiling&
     at[0].val.programmaticStreamSerializationAllowed = 1;
     lc.attrs = at;
     lc.numAttrs = 1;
-    cudaLaunchKernelEx(&lc, k_boundary<D, Op>, tl, a, tile_grid<Op>(tl, split));
+    cudaLaunchKernelEx(&lc, k_boundary<D, Op>, tl, a, tile_grid<Op>(tl, split, persist));
 #else
-    k_boundary<D, Op><<<nb, kBoundaryBlock, 0, c.stream>>>(tl, a, tile_grid<Op>(tl, split));
+    k_boundary<D, Op><<<nb, kBoundaryBlock, 0, c.stream>>>(tl, a, tile_grid<Op>(tl, split, persist));
 #endif
     note_launch(name, c.stream);
   }
