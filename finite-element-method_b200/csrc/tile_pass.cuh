@@ -406,13 +406,14 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile(DevTiling tl, 
 
 constexpr int kBoundaryBlock = 256;
 
-template <int D, class Op>
+// FUSE: multi-GPU launches whose halo exchange is received here (the single-GPU instantiation carries none of it)
+template <int D, class Op, bool FUSE>
 __global__ void __launch_bounds__(kBoundaryBlock) k_boundary(DevTiling tl, typename Op::Args a, int red_base) {
   __shared__ float s_warp[32];
   // multi-GPU, exchange fused into this kernel: the neighbours' sums of the shared vertices are read straight
   // from the receive plane they stored into (no unpack kernel).  The sequence bookkeeping runs even when the
   // solver has already converged, so that all ranks keep counting the same exchanges.
-  const HaloDev* hd = tl.fuse_recv ? tl.hd : nullptr;
+  const HaloDev* hd = FUSE ? tl.hd : nullptr;
   uint32_t rseq = 0, rparity = 0;
   if (hd) rparity = halo_recv_begin(hd->pc, rseq);
   if (Op::early_exit(a)) {
@@ -423,7 +424,7 @@ __global__ void __launch_bounds__(kBoundaryBlock) k_boundary(DevTiling tl, typen
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b < tl.n_boundary) {
     const float4* part = Op::partial_buf(a);
-    const int hk = hd ? hd->bhalo[b] : -1;          // >= 0: shared vertex, its last slot is the remote one
+    const int hk = FUSE ? hd->bhalo[b] : -1;        // >= 0: shared vertex, its last slot is the remote one
     const int s0 = tl.bptr[b], s1 = tl.bptr[b + 1] - (hk >= 0 ? 1 : 0);
     const int gid = tl.n_interior + b;
     // the vertex operands do not depend on the partial sums: request them first
@@ -551,9 +552,12 @@ inline void run_tile_pass(const char* name, const LaunchCfg& c, const DevTiling&
     at[0].val.programmaticStreamSerializationAllowed = 1;
     lc.attrs = at;
     lc.numAttrs = 1;
-    cudaLaunchKernelEx(&lc, k_boundary<D, Op>, tl, a, tile_grid<Op>(tl, split, persist));
+    cudaLaunchKernelEx(&lc, k_boundary<D, Op, false>, tl, a, tile_grid<Op>(tl, split, persist));
 #else
-    k_boundary<D, Op><<<nb, kBoundaryBlock, 0, c.stream>>>(tl, a, tile_grid<Op>(tl, split, persist));
+    if (tl.fuse_recv && tl.hd)
+      k_boundary<D, Op, true><<<nb, kBoundaryBlock, 0, c.stream>>>(tl, a, tile_grid<Op>(tl, split, persist));
+    else
+      k_boundary<D, Op, false><<<nb, kBoundaryBlock, 0, c.stream>>>(tl, a, tile_grid<Op>(tl, split, persist));
 #endif
     note_launch(name, c.stream);
   }
