@@ -160,15 +160,21 @@ def test_implicit_solve_driver_gloo_world2():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("comm", ["peer", "nccl"])
-def test_two_rank_slabs_match_single_gpu(comm):
-    """comm=peer: halo sums / dot products inside the library's kernels over NVLink peer memory;
-    comm=nccl: the same phases driven from Python with torch.distributed P2P + all_reduce."""
+@pytest.mark.parametrize("comm,extra", [
+    ("peer", {}),                                   # exchange fused into the pass's own kernels (default)
+    ("peer", {"FEMB_PEER_FUSED_WAVES": "0"}),       # thick-slab variant: persistent operator kernels + send kernel
+    ("peer", {"FEMB_PEER_FUSED": "0"}),             # separate send / receive / reduce kernels
+    ("nccl", {}),
+])
+def test_two_rank_slabs_match_single_gpu(comm, extra):
+    """comm=peer: halo sums / dot products inside the library's kernels over NVLink peer memory (all three
+    kernel arrangements of csrc/object.h: peer_pass); comm=nccl: the same phases driven from Python with
+    torch.distributed P2P + all_reduce."""
     import torch
 
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
-    env = dict(os.environ, FEMB200_COMM=comm)
+    env = dict(os.environ, FEMB200_COMM=comm, **extra)
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
                         "--master-addr", "127.0.0.1", "--master-port", "29611",
                         os.path.join(ROOT, "tests", "mp_slab_check.py")], capture_output=True, text=True, timeout=180,
