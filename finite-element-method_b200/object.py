@@ -10,6 +10,8 @@ Mesh sources (config dict of one entry of "objects"):
                                                       by femb200.meshio -- TetGen itself is a
                                                       third-party C++ package that is not available)
             "cells": [nx, ny, nz] + "h"              (extension: structured Kuhn tet box)
+            "side_length" + "subdivisions", no "obj" (extension, SURVEY.md 8 f1: the 2D keys in 3D --
+                                                      a Kuhn cube of subdivisions^3 cells)
   any dim : Object.from_arrays(config, vertices, elements)   (extension: bring your own mesh)
 """
 import numpy as np
@@ -85,6 +87,9 @@ class Object:
         if config.get('cells') is not None:
             nx, ny, nz = config.get('cells')
             vertices, elements = meshgen.kuhn_box(nx, ny, nz, config.get('h'))
+        elif config.get('obj') is None and config.get('side_length') and config.get('subdivisions'):
+            n = int(config.get('subdivisions'))
+            vertices, elements = meshgen.kuhn_box(n, n, n, config.get('side_length') / n)
         else:
             from femb200 import meshio
             vertices, elements, self.surface_source = meshio.tetrahedralize_file(config.get('obj'))

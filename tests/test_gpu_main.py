@@ -37,6 +37,7 @@ def _cfg(tmp_path, base, name="cfg.json", **edits):
     ("default.json", {}, "explicit method. Auto-diff True"),
     ("config/default_analytic.json", {}, "explicit method. Auto-diff False"),
     ("config/demo_3d_blob.json", {"is_output_obj": True}, "explicit method. Auto-diff False"),
+    ("config/demo_3d_cube.json", {}, "explicit method. Auto-diff False"),
     ("config/demo_3d_implicit_blob.json", {}, "conjugate gradient. Preconditioned: True"),
     ("config/demo_3d_implicit_blob.json", {"preconditioned": 0}, "conjugate gradient. Preconditioned: False"),
     ("config/demo_3d_implicit_blob.json", {"implicit_method": 0, "delta_time": 1e-4}, "jacobian iteration"),
