@@ -33,6 +33,55 @@ class VertexField:
         return (self._obj.particle_cnt,)
 
 
+class DenseOperator:
+    """Debug densifier for obj.matrix_A / matrix_AT / matrix_ATA (reference object.py:82,91,92; read in the
+    commented debug block of main.py:14-28).  The solver never forms these Nv x Nv block matrices (108 Nv^2
+    bytes); for SMALL meshes `.to_numpy()` builds [Nv, Nv, dim, dim] column by column from the matrix-free
+    operator at the CURRENT positions (femb_implicit_assemble + femb_implicit_apply on unit vectors):
+    block [i, j][:, k] = (A e_{j,k})_i.  matrix_ATA follows implicit.py:289-307: A^T A when
+    constants.preconditioned == 1, else A itself."""
+
+    MAX_VERTICES = 2000
+
+    def __init__(self, obj, kind):
+        self._obj, self._kind = obj, kind
+
+    @property
+    def shape(self):
+        return (self._obj.particle_cnt, self._obj.particle_cnt)
+
+    def to_numpy(self, dt=None):
+        import constants
+        obj, nv = self._obj, self._obj.particle_cnt
+        if nv > self.MAX_VERTICES:
+            raise RuntimeError("dense {} is a debug aid for <= {} vertices (this object has {}): the operator is "
+                               "matrix-free".format(self._kind, self.MAX_VERTICES, nv))
+        dt = constants.delta_time if dt is None else dt
+        dim = obj._h.dim
+        obj._h.implicit_assemble(dt)
+        A = np.empty((nv, nv, dim, dim), np.float32)
+        e = np.zeros((nv, dim), np.float32)
+
+        def column(j, k):
+            e[j, k] = 1.0
+            if self._kind == 'matrix_AT':
+                y = obj._h.implicit_apply(dt, e, transpose=True)
+            else:
+                y = obj._h.implicit_apply(dt, e)
+                if self._kind == 'matrix_ATA' and constants.preconditioned == 1:
+                    y = obj._h.implicit_apply(dt, y, transpose=True)
+            e[j, k] = 0.0
+            return y
+
+        for j in range(nv):
+            for k in range(dim):
+                A[:, j, :, k] = column(j, k)
+        return A
+
+    def __getitem__(self, ij):
+        return self.to_numpy()[ij]
+
+
 class Particles:
     """obj.particles.<member> with the reference's Particle struct names (object.py:12-23)."""
 

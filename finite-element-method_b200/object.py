@@ -54,6 +54,10 @@ class Object:
             self.vec_b = fields.VertexField(self, _capi.F_VEC_B, writable=False)
             self.vec_x = fields.VertexField(self, _capi.F_VEC_X)
             self.past_vec_x = fields.VertexField(self, _capi.F_PAST_X)
+            # dense matrices are never formed; debug densifiers for small meshes only (object.py:82,91,92)
+            self.matrix_A = fields.DenseOperator(self, 'matrix_A')
+            self.matrix_AT = fields.DenseOperator(self, 'matrix_AT')
+            self.matrix_ATA = fields.DenseOperator(self, 'matrix_ATA')
         # extension (synthetic benchmark meshes): initial state x = X + jitter * h * U(-1, 1)
         if config.get('jitter'):
             rng = np.random.default_rng(config.get('seed', 0))
