@@ -139,3 +139,64 @@ def test_large_structured_tiling_stats():
     assert info["n_tiles"] >= len(el) // 768 and info["stage_stride"] >= 768
     assert info["max_rounds"] == 24            # interior Kuhn valence
     assert info["n_boundary"] < 0.75 * len(verts)
+
+
+@pytest.mark.parametrize("dim,n_pts,T,seed", [(2, 400, 64, 1), (2, 1500, 256, 2), (3, 300, 128, 3), (3, 900, 768, 4)])
+def test_tiling_unstructured_delaunay_with_halo_and_waves(dim, n_pts, T, seed):
+    """Irregular valences (Delaunay of random points), shared (halo) vertices and whole-wave tile counts:
+    gather == scatter still holds, halo vertices are boundary vertices with ONE extra (remote) partial slot,
+    and the tiles that touch them come first (the multi-GPU pass sends after those)."""
+    from scipy.spatial import Delaunay
+
+    rng = np.random.default_rng(seed)
+    pts = rng.uniform(0, 1, (n_pts, dim))
+    el = Delaunay(pts).simplices.astype(np.int32)
+    used = np.unique(el)                                  # Delaunay can leave coplanar/duplicate points unused
+    remap = np.full(n_pts, -1, np.int32)
+    remap[used] = np.arange(used.size, dtype=np.int32)
+    verts, el = pts[used].astype(np.float32), remap[el]
+    nc = dim + 1
+    halo = np.nonzero(verts[:, 0] > 0.9)[0].astype(np.int32)          # a "right interface" of the point cloud
+    t0 = _capi.HostTiling(verts, el, T)
+    t = _capi.HostTiling(verts, el, T, halo_verts=halo, wave=4)
+    info = t.info
+    assert info["n_interior"] + info["n_boundary"] == len(verts)
+    assert info["n_tiles"] >= t0.info["n_tiles"] or info["n_tiles"] % 4 == 0
+    new_of_old = t.array(0)
+    assert np.array_equal(np.sort(new_of_old), np.arange(len(verts)))
+    assert len(np.unique(t.array(1))) == len(el)
+    tiles = t.array(2).reshape(-1, 12)
+    assert tiles[:, 1].sum() == len(el) and tiles[:, 1].max() <= T and tiles[:, 1].min() >= 1
+    # halo vertices: boundary numbering, exactly one slot more than without the halo flag
+    n_int = info["n_interior"]
+    bptr = t.array(7)
+    hb = new_of_old[halo] - n_int
+    assert (hb >= 0).all()
+    assert info["n_partials"] == bptr[-1]
+    lv = t.array(3).reshape(-1, 2)
+    rows = np.concatenate([lv[o_:o_ + n] for (_s, _n, o_, n, *_r) in tiles])      # (the table is padded between tiles)
+    slots_written = np.bincount(rows[rows[:, 1] >= 0, 1], minlength=info["n_partials"])
+    assert slots_written.max() == 1                        # every partial slot has exactly one writer ...
+    free = np.nonzero(slots_written == 0)[0]               # ... except the remote slots, written by the exchange
+    assert np.array_equal(np.sort(free), np.sort(bptr[hb + 1] - 1))
+    # the tiles that touch a halo vertex are the first n_halo_tiles tiles
+    is_halo_new = np.zeros(len(verts), bool)
+    is_halo_new[new_of_old[halo]] = True
+    touches = np.array([is_halo_new[lv[o_:o_ + n, 0]].any() for (_s, _n, o_, n, *_r) in tiles])
+    nh = info["n_halo_tiles"]
+    assert touches[:nh].all() and not touches[nh:].any() and 0 < nh <= info["n_tiles"]
+    vals = rng.standard_normal((len(el), nc, 3))
+    want = np.zeros((len(verts), 3))
+    for c in range(nc):
+        np.add.at(want, el[:, c], vals[:, c])
+    assert np.allclose(_emulate(t, nc, vals), want, rtol=1e-12, atol=1e-12)
+
+
+def test_tiling_single_element_and_tiny_meshes():
+    for dim in (2, 3):
+        verts = np.eye(dim + 1, dim, k=-1, dtype=np.float32)          # origin + unit vectors
+        el = np.arange(dim + 1, dtype=np.int32)[None, :]
+        t = _capi.HostTiling(verts, el, 64)
+        assert t.info["n_tiles"] == 1 and t.info["n_boundary"] == 0 and t.info["n_interior"] == dim + 1
+        vals = np.arange((dim + 1) * 3, dtype=float).reshape(1, dim + 1, 3)
+        assert np.allclose(_emulate(t, dim + 1, vals), vals[0])
