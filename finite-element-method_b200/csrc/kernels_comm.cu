@@ -1,4 +1,5 @@
 // kernels_comm.cu -- multi-GPU communication INSIDE our kernels, over NVLink peer memory.
+// (New: the reference runs on one device, main.py:40 / utils.py:12-17; SURVEY.md 8e defines the slab partition.)
 //
 // One process per GPU; every rank owns one symmetric "comm buffer" that all ranks have mapped
 // (torch symmetric memory / CUDA IPC on the host side, femb_peer_bind).  No NCCL call sits on the

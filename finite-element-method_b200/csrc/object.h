@@ -1,4 +1,5 @@
-// object.h -- the host-side object behind the opaque femb_object handle.
+// object.h -- the host-side object behind the opaque femb_object handle: what the reference keeps in the Taichi
+// fields of object.Object (object.py:52-93) plus the launch state (streams, CUDA graphs, multi-GPU exchange).
 #pragma once
 #include <cuda_runtime.h>
 
