@@ -206,3 +206,39 @@ def test_advect_implicit_upper_wall_keeps_vel_g():
     assert vel[0, 1] == 0 and vel_g[0, 1] == 2.0   # implicit.py:420-423
     assert vel[1, 1] == 0 and vel_g[1, 1] == 0.0   # implicit.py:415-418
     assert pos[0, 1] == np.float32(1.5) and pos[1, 1] == np.float32(-0.5)
+
+
+@pytest.mark.parametrize("maker", [_cube, _square])
+def test_homogeneous_deformation_matches_closed_form_neo_hookean(maker):
+    """Known-answer test that does not come from the restatement itself: under a homogeneous deformation
+    x = F X of the whole body, linear elements reproduce F exactly, so with
+        phi(F) = mu/2 (tr F^T F - dim) - mu ln J + lambda/2 (ln J)^2,   P(F) = mu (F - F^-T) + lambda ln J F^-T
+    (the energy of explicit_auto_diff.py:26-28 and its first Piola stress, explicit.py:25-28)
+        U = V_body phi(F),   sum_v g_v X_v^T = V_body P(F)   (virtual work, g = dU/dx),
+    and every vertex strictly inside the body is in equilibrium (g_v = 0)."""
+    pos0, _, el, ref, vol, _ = maker(dtype=np.float64)
+    dim = pos0.shape[1]
+    F = np.array([[1.20, 0.10, 0.00], [0.00, 0.90, 0.05], [0.03, 0.00, 1.10]])[:dim, :dim]
+    pos = pos0 @ F.T
+    J = np.linalg.det(F)
+    FinvT = np.linalg.inv(F).T
+    phi = MU / 2 * (np.trace(F.T @ F) - dim) - MU * np.log(J) + LAM / 2 * np.log(J) ** 2
+    P = MU * (F - FinvT) + LAM * np.log(J) * FinvT
+    V = vol.sum()
+    _, U = o.compute_energy(pos, el, ref, vol, MU, LAM)
+    assert abs(U - V * phi) <= 1e-12 * abs(V * phi)
+    g = np.zeros_like(pos)
+    o.neo_hookean_1_grad(pos, el, ref, vol, MU, LAM, g)            # "force" = +dU/dx (explicit.py:42-49)
+    assert rel((g[:, :, None] * pos0[:, None, :]).sum(axis=0), V * P) <= 1e-11
+    lo, hi = pos0.min(axis=0), pos0.max(axis=0)
+    inside = np.all((pos0 > lo + 1e-9) & (pos0 < hi - 1e-9), axis=1)
+    assert inside.sum() > 0 and np.abs(g[inside]).max() <= 1e-9 * np.abs(g).max()
+    # the autodiff oracle agrees with the same closed form
+    _, ga = o.energy_autograd(pos, el, ref, vol, MU, LAM, dtype=np.float64)
+    assert rel((ga[:, :, None] * pos0[:, None, :]).sum(axis=0), V * P) <= 1e-11
+    # fp32 on the same inputs: within the tolerance the GPU parity tests use
+    p32, r32, v32 = pos.astype(np.float32), ref.astype(np.float32), vol.astype(np.float32)
+    g32, g64 = np.zeros(pos.shape, np.float32), np.zeros(pos.shape)
+    o.neo_hookean_1_grad(p32, el, r32, v32, MU, LAM, g32)
+    o.neo_hookean_1_grad(p32.astype(np.float64), el, r32.astype(np.float64), v32.astype(np.float64), MU, LAM, g64)
+    assert rel(g32, g64) <= 1e-5
