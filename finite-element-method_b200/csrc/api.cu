@@ -49,7 +49,9 @@ KinArgs femb_object::kin_args(float dt, const float* g_dir) const {
 static const int kMaxSmem = 226 * 1024;  // 227 KB per CTA minus the kernels' static shared memory
 
 static int tile_smem_bytes(const Tiling& t) {
-  return tile_smem_layout(t.max_lv, (t.max_rounds + 3) / 4 * 4, t.nc, (t.dim + 1) * t.dim).total;
+  // largest layout any Op uses: D*D + D staging planes; the second vertex buffer only when an Op with
+  // ASYNC_VERTEX is built persistent (FEMB_PERSIST_EXPLICIT, off by default)
+  return tile_smem_layout(t.max_lv, (t.max_rounds + 3) / 4 * 4, t.nc, (t.dim + 1) * t.dim, FEMB_PERSIST_EXPLICIT != 0).total;
 }
 
 extern "C" {

@@ -59,10 +59,12 @@ struct DevTiling {
 //   rounds  [max_rounds] uint32    bulk-copied JDS round counts
 //   jds     [nc*stage_stride] u16  bulk-copied JDS entries
 //   stage   [n_planes][stage_stride] float
+//   sv2     [max_lv] float4        (two_sv only) vertex values of the CTA's NEXT tile, filled by cp.async
 struct TileSmem {
-  int lvt, lvt2, rounds, jds, stage, total;   // lvt2: second local-vertex table (the CTA's next tile)
+  int lvt, lvt2, rounds, jds, stage, sv2, total;   // lvt2: second local-vertex table (the CTA's next tile)
 };
-__host__ __device__ inline TileSmem tile_smem_layout(int max_lv, int max_rounds, int nc, int n_planes) {
+__host__ __device__ inline TileSmem tile_smem_layout(int max_lv, int max_rounds, int nc, int n_planes,
+                                                     bool two_sv = false) {
   TileSmem s;
   int off = max_lv * 16;
   s.lvt = off;    off += (max_lv * 8 + 15) / 16 * 16;
@@ -70,6 +72,7 @@ __host__ __device__ inline TileSmem tile_smem_layout(int max_lv, int max_rounds,
   s.rounds = off; off += (max_rounds * 4 + 15) / 16 * 16;
   s.jds = off;    off += (nc * kStride * 2 + 15) / 16 * 16;
   s.stage = off;  off += n_planes * kStride * 4;
+  s.sv2 = off;    off += two_sv ? max_lv * 16 : 0;   // last: the other offsets do not depend on it
   s.total = off;
   return s;
 }

@@ -65,6 +65,7 @@ __device__ __forceinline__ void kinematic_update(float4& p, float4& v, const flo
 template <int D>
 struct OpSetup {
   static constexpr bool PERSIST = false;
+  static constexpr bool ASYNC_VERTEX = false;
   static constexpr int BLOCK = kBlock, MIN_CTAS = kMinCtas,NSTAGE = 1, GATHER = G_UNIFORM;
   static constexpr bool REDUCE = false;
   struct Args {
@@ -151,6 +152,9 @@ struct OpSetup {
 template <int D, int MODE>
 struct OpExplicit {
   static constexpr bool PERSIST = FEMB_PERSIST_EXPLICIT != 0;
+  // the tile's vertex values are pos[gid] untransformed: the persistent kernel fetches the NEXT tile's values
+  // global -> shared with cp.async into a second vertex buffer (no registers held across the element phase)
+  static constexpr bool ASYNC_VERTEX = true;
   static constexpr int BLOCK = kBlock, MIN_CTAS = kMinCtas,NSTAGE = D * D, GATHER = G_STAR;
   static constexpr bool REDUCE = (MODE == EX_ENERGY);
   struct Args {
@@ -166,6 +170,7 @@ struct OpExplicit {
   __device__ static float4* partial_buf(const Args& a) { return a.vs.partial; }
   __device__ static double* red_buf(const Args& a) { return a.red; }
   __device__ static float4 load_vertex(const Args& a, int gid) { return a.vs.pos[gid]; }
+  __device__ static const float4* vertex_src(const Args& a) { return a.vs.pos; }   // ASYNC_VERTEX source array
 
   using Elem = PlaneElem;
   __device__ static void prefetch(const Args& a, int slot, uint32_t bytes) { prefetch_planes(a.e, slot, bytes, D == 3); }

@@ -18,6 +18,7 @@ namespace femb {
 template <int D>
 struct OpAssemble {
   static constexpr bool PERSIST = FEMB_PERSIST_ASSEMBLE != 0;
+  static constexpr bool ASYNC_VERTEX = false;
   static constexpr int BLOCK = kBlock, MIN_CTAS = kMinCtas,NSTAGE = D * D, GATHER = G_STAR;
   static constexpr bool REDUCE = false;
   struct Args {
@@ -115,6 +116,7 @@ struct OpAssemble {
 template <int D>
 struct OpDiag {
   static constexpr bool PERSIST = FEMB_PERSIST_APPLY != 0;
+  static constexpr bool ASYNC_VERTEX = false;
   static constexpr int BLOCK = kBlock, MIN_CTAS = kMinCtas,NSTAGE = D, GATHER = G_UNIFORM;
   static constexpr bool REDUCE = false;
   struct Args {
@@ -153,6 +155,7 @@ struct OpDiag {
 template <int D, int TR>
 struct OpApply {
   static constexpr bool PERSIST = FEMB_PERSIST_APPLY != 0;
+  static constexpr bool ASYNC_VERTEX = false;
   static constexpr int BLOCK = kBlock, MIN_CTAS = kMinCtas,NSTAGE = D * D, GATHER = G_STAR;
   static constexpr bool REDUCE = true;
   struct Args {

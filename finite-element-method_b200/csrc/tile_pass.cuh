@@ -184,9 +184,11 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile_persistent(Dev
   int t = t_begin + bid;
   if (t >= t_end) return;
   constexpr int S = kStride;
-  const TileSmem lay = tile_smem_layout(tl.max_lv, tl.max_rounds, tl.nc, n_planes<D, Op>());
+  constexpr bool AV = Op::ASYNC_VERTEX;   // next tile's vertex values by cp.async into a second buffer
+  const TileSmem lay = tile_smem_layout(tl.max_lv, tl.max_rounds, tl.nc, n_planes<D, Op>(), AV);
   char* smem = reinterpret_cast<char*>(smem4);
-  float4* sv = smem4;
+  float4* const sv0 = smem4;
+  float4* const sv1 = AV ? reinterpret_cast<float4*>(smem + lay.sv2) : smem4;
   auto lv_buf = [&](int i) { return reinterpret_cast<LocalVert*>(smem + (i ? lay.lvt2 : lay.lvt)); };
   uint32_t* s_rounds = reinterpret_cast<uint32_t*>(smem + lay.rounds);
   uint16_t* s_jds = reinterpret_cast<uint16_t*>(smem + lay.jds);
@@ -209,7 +211,11 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile_persistent(Dev
   // vertex values of the tile about to be processed: two per thread in registers, the rest (tiles with
   // more than 2*B local vertices: irregular meshes only) fetched directly at staging time
   float4 vreg0 = make_float4(0.f, 0.f, 0.f, 0.f), vreg1 = vreg0;
-  {
+  if constexpr (AV) {
+    const int n_lv = s_td[0].n_lv;
+    for (int l = tid; l < n_lv; l += B) cp_async16(&sv0[l], Op::vertex_src(a) + lv_buf(0)[l].gid);
+    cp_async_commit();
+  } else {
     const int n_lv = s_td[0].n_lv;
     if (tid < n_lv) vreg0 = Op::load_vertex(a, lv_buf(0)[tid].gid);
     if (tid + B < n_lv) vreg1 = Op::load_vertex(a, lv_buf(0)[tid + B].gid);
@@ -220,6 +226,7 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile_persistent(Dev
     const int b = k & 1;
     const DevTile& td = s_td[b];          // read on demand from shared memory (keeps registers for the math)
     const LocalVert* s_lv = lv_buf(b);
+    float4* const sv = (AV && b) ? sv1 : sv0;
     const int n_elem = td.n_elem, slot_off = td.slot_off;
     const int tn = t + G;
     const bool has_next = tn < t_end;
@@ -244,9 +251,13 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile_persistent(Dev
     if (tid < n_elem) Op::load(a, slot_off + tid, d0);
     if (tid + B < n_elem) Op::load(a, slot_off + tid + B, d1);
 
-    if (tid < td.n_lv) sv[tid] = vreg0;
-    if (tid + B < td.n_lv) sv[tid + B] = vreg1;
-    for (int l = tid + 2 * B; l < td.n_lv; l += B) sv[l] = Op::load_vertex(a, s_lv[l].gid);
+    if constexpr (AV) {
+      cp_async_wait_all();               // this thread's copies have landed; the barrier publishes everyone's
+    } else {
+      if (tid < td.n_lv) sv[tid] = vreg0;
+      if (tid + B < td.n_lv) sv[tid + B] = vreg1;
+      for (int l = tid + 2 * B; l < td.n_lv; l += B) sv[l] = Op::load_vertex(a, s_lv[l].gid);
+    }
     __syncthreads();
 
     auto one = [&](int e, const typename Op::Elem& d) {
@@ -270,8 +281,15 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile_persistent(Dev
       mbar_wait(&s_bar[b ^ 1], (uint32_t)(((k + 1) >> 1) & 1));
       const int n_lv = s_td[b ^ 1].n_lv;
       const LocalVert* nlv = lv_buf(b ^ 1);
-      if (tid < n_lv) vreg0 = Op::load_vertex(a, nlv[tid].gid);
-      if (tid + B < n_lv) vreg1 = Op::load_vertex(a, nlv[tid + B].gid);
+      if constexpr (AV) {
+        // the other vertex buffer held tile k-1, whose gather ended before the barrier that closed iteration k-1
+        float4* const svn = b ? sv0 : sv1;
+        for (int l = tid; l < n_lv; l += B) cp_async16(&svn[l], Op::vertex_src(a) + nlv[l].gid);
+        cp_async_commit();
+      } else {
+        if (tid < n_lv) vreg0 = Op::load_vertex(a, nlv[tid].gid);
+        if (tid + B < n_lv) vreg1 = Op::load_vertex(a, nlv[tid + B].gid);
+      }
     }
     mbar_wait(&s_bar[2], (uint32_t)(k & 1));
 
@@ -492,12 +510,15 @@ inline void run_tile_pass(const char* name, const LaunchCfg& c, const DevTiling&
   tl.hd = c.hd;
   tl.n_send = 0;
   tl.fuse_recv = 0;
-  static int attr_set[64] = {};  // per device (the attribute lives in the device's context): bytes allowed so far
-  const int smem = tile_smem_layout(tl.max_lv, tl.max_rounds, tl.nc, n_planes<D, Op>()).total;
+  // bytes of dynamic shared memory allowed so far, per kernel function (persistent / one CTA per tile) and per
+  // device (the attribute lives in the device's context)
+  static int attr_set_all[2][64] = {};
   // Persistent CTAs own a fixed share of the tiles, so sender CTAs that hold SM slots at the start would make
   // the tile CTAs that wait for those slots finish late: fused multi-GPU passes use one CTA per tile.
   const bool persist = Op::PERSIST && !c.no_persist;
+  const int smem = tile_smem_layout(tl.max_lv, tl.max_rounds, tl.nc, n_planes<D, Op>(), persist && Op::ASYNC_VERTEX).total;
   auto* kern = persist ? k_tile_persistent<D, Op> : k_tile<D, Op>;
+  int* attr_set = attr_set_all[persist ? 1 : 0];
   if (smem > attr_set[c.device & 63]) {
     const cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) {
