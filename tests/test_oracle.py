@@ -242,3 +242,25 @@ def test_homogeneous_deformation_matches_closed_form_neo_hookean(maker):
     o.neo_hookean_1_grad(p32, el, r32, v32, MU, LAM, g32)
     o.neo_hookean_1_grad(p32.astype(np.float64), el, r32.astype(np.float64), v32.astype(np.float64), MU, LAM, g64)
     assert rel(g32, g64) <= 1e-5
+
+
+def test_free_fall_with_damping_matches_closed_form():
+    """Known answer for the integrator (kinematic.py:15-23, 43): with no elastic force the update is
+    v <- (v + g dt) q,  x <- x + v dt,  q = exp(-dt c), so after n steps
+    v_n = g dt q (1 - q^n) / (1 - q)   and   x_n = x_0 + dt * sum_k v_k  (geometric sums)."""
+    dt, c, n = 5e-4, 14.5, 400
+    g = np.array([0.0, -1.0])
+    pos = np.array([[0.5, 0.9]], dtype=np.float64)
+    vel = np.zeros_like(pos)
+    mass = np.ones(1)
+    for _ in range(n):
+        o.kinematic(pos, vel, np.zeros_like(pos), mass, dt, g, c, [], auto_diff=0)
+    q = np.exp(-dt * c)
+    a = 9.8 * g * dt
+    v_n = a * q * (1 - q ** n) / (1 - q)
+    # sum_{k=1..n} v_k = a q / (1 - q) * (n - q (1 - q^n) / (1 - q))
+    x_n = np.array([0.5, 0.9]) + dt * a * q / (1 - q) * (n - q * (1 - q ** n) / (1 - q))
+    assert np.allclose(vel[0], v_n, rtol=1e-12, atol=0) or np.allclose(vel[0], v_n, atol=1e-15)
+    assert np.allclose(pos[0], x_n, rtol=1e-12)
+    # terminal velocity g / c is approached from below (damping 14.5 of default.json: 0.676 m/s)
+    assert abs(vel[0, 1]) < 9.8 / c and abs(vel[0, 1]) > 0.9 * 9.8 / c * (1 - q ** n)
