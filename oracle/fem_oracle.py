@@ -182,8 +182,8 @@ def elements_init(pos, elems, rho):
     volume = compute_volume(r)
     mass = np.zeros(pos.shape[0], dtype=pos.dtype)
     contrib = dt(1.0 / (dim + 1)) * volume * dt(rho)
-    for j in range(dim + 1):
-        np.add.at(mass, elems[:, j], contrib)
+    # element by element, corners j = 0..dim (the serial order of object.py:357-360; np.add.at is unbuffered)
+    np.add.at(mass, elems.reshape(-1), np.repeat(contrib, dim + 1))
     ref = _inverse(r)
     return ref, volume, mass
 
@@ -208,11 +208,15 @@ def scatter_gradient(G, elems, out):
     """explicit.py:42-49 -- out[v_{j+1}] += G[:, j]; out[v_0] += -sum_j G[:, j]."""
     dim = out.shape[1]
     f0 = np.zeros((elems.shape[0], dim), dtype=out.dtype)
+    vals = np.empty((elems.shape[0], dim + 1, dim), dtype=out.dtype)
     for j in range(dim):
         f = G[:, :, j]
-        np.add.at(out, elems[:, j + 1], f)
+        vals[:, j] = f
         f0 = f0 - f
-    np.add.at(out, elems[:, 0], f0)
+    vals[:, dim] = f0
+    # element by element: corners 1..dim, then corner 0 (the serial order of explicit.py:42-49)
+    order = list(range(1, dim + 1)) + [0]
+    np.add.at(out, elems[:, order].reshape(-1), vals.reshape(-1, dim))
     return out
 
 
@@ -330,7 +334,7 @@ def element_hessian_block(pos, elems, ref, volume, mu, s_lambda):
     for k in range(1, dim):
         tr = tr + FiR[:, k, k]
     term = ft(mu) * dF \
-        + (ft(mu) - ft(s_lambda) * log_j)[:, None, None] * _matmul(_matmul(F_inv_T, dF_T), F_inv_T) \
+        + _matmul(_matmul((ft(mu) - ft(s_lambda) * log_j)[:, None, None] * F_inv_T, dF_T), F_inv_T) \
         + (ft(s_lambda) * tr)[:, None, None] * F_inv_T
     H = _matmul((-volume)[:, None, None] * term, _transpose(ref))
     return H
@@ -346,21 +350,33 @@ def compute_linear_system_matrix_a(pos, elems, ref, volume, mass, mu, s_lambda, 
     H = element_hessian_block(pos, elems, ref, volume, mu, s_lambda)
     A = np.zeros((nv, nv, dim, dim), dtype=pos.dtype)
     v0 = elems[:, 0]
+    ne = elems.shape[0]
     H00 = np.zeros_like(H)
-    for i in range(dim):
+    rows, cols, blks = [], [], []
+    for i in range(dim):                   # element by element, in the order the reference's loop issues its adds
         vi = elems[:, i + 1]
-        np.add.at(A, (vi, vi), H)          # implicit.py:151
-        np.add.at(A, (vi, v0), -H)         # implicit.py:155,161
-        np.add.at(A, (v0, vi), -H)         # implicit.py:157,178
+        rows += [vi, vi]
+        cols += [vi, v0]
+        blks += [H, -H]                    # implicit.py:151 (i == j), 161 (dF_dxi0 = 0 - ... - H)
         H00 = H00 + H                      # implicit.py:149
-    np.add.at(A, (v0, v0), H00)            # implicit.py:168
-    dt2 = ft(dt) ** 2
-    inv_m = ft(1.0) / mass
-    A = dt2 * inv_m[:, None, None, None] * A          # implicit.py:183-187
-    eye = np.eye(dim, dtype=pos.dtype)
-    A = -A
-    A[np.arange(nv), np.arange(nv)] += eye           # implicit.py:189-194
-    return A
+    rows.append(v0)
+    cols.append(v0)
+    blks.append(H00)                       # implicit.py:168
+    for i in range(dim):
+        rows.append(v0)
+        cols.append(elems[:, i + 1])
+        blks.append(-H)                    # implicit.py:157,178 (temp block = 0 - ... - H)
+    rows = np.stack(rows, 1).reshape(-1)
+    cols = np.stack(cols, 1).reshape(-1)
+    blks = np.stack(blks, 1).reshape(ne * len(blks), dim, dim)
+    np.add.at(A, (rows, cols), blks)
+    # implicit.py:183-187: (dt**2 [python double] * ((1/m) * eye)) @ A[i,j]  ==  f32(f32(dt^2) * (1/m)) * A[i,j]
+    scale = ft(float(dt) ** 2) * (ft(1.0) / mass)
+    A = scale[:, None, None, None] * A
+    # implicit.py:189-194: A = I - A  (off-diagonal entries become 0 - a)
+    eye = np.zeros((nv, nv, dim, dim), dtype=pos.dtype)
+    eye[np.arange(nv), np.arange(nv)] = np.eye(dim, dtype=pos.dtype)
+    return eye - A
 
 
 def internal_force_implicit(pos, elems, ref, volume, mu, s_lambda):
@@ -382,56 +398,81 @@ def compute_linear_system_vector_b(pos, vel, elems, ref, volume, mass, mu, s_lam
     b = vel.copy()
     G = internal_force_implicit(pos, elems, ref, volume, mu, s_lambda)
     f0 = np.zeros((elems.shape[0], dim), dtype=pos.dtype)
+    vals = np.empty((elems.shape[0], dim + 1, dim), dtype=pos.dtype)
     for i in range(dim):
         f_n = G[:, :, i]
         f0 = f0 - f_n
-        idx = elems[:, i + 1]
-        m_ = ft(1.0) / mass[idx]
-        np.add.at(b, idx, (ft(dt) * m_)[:, None] * f_n)
-    idx = elems[:, 0]
-    m_ = ft(1.0) / mass[idx]
-    np.add.at(b, idx, (ft(dt) * m_)[:, None] * f0)
+        m_ = ft(1.0) / mass[elems[:, i + 1]]
+        vals[:, i] = (ft(dt) * m_)[:, None] * f_n
+    m_ = ft(1.0) / mass[elems[:, 0]]
+    vals[:, dim] = (ft(dt) * m_)[:, None] * f0
+    order = list(range(1, dim + 1)) + [0]              # element by element: corners 1..dim, then 0 (implicit.py:92-105)
+    np.add.at(b, elems[:, order].reshape(-1), vals.reshape(-1, dim))
     return b
 
 
+def _block_terms(A, x):
+    """t[i, j, :] = A[i, j] @ x[j] with Taichi's matmul order (k ascending)."""
+    t = A[..., 0] * x[None, :, None, 0]
+    for k in range(1, x.shape[1]):
+        t = t + A[..., k] * x[None, :, None, k]
+    return t
+
+
 def _dense_matvec(A, x):
-    """sum_j A[i,j] @ x[j], j ascending is approximated by einsum (order-insensitive use only)."""
-    return np.einsum("ijkl,jl->ik", A, x)
+    """v[i] = ((0 + A[i,0] @ x[0]) + A[i,1] @ x[1]) + ...  -- j ascending, one add per block, exactly the serial
+    order of implicit.py:281-282, 347-349 (ufunc.accumulate is sequential)."""
+    return np.add.accumulate(_block_terms(A, x), axis=1)[:, -1]
+
+
+def _seq_sum(v):
+    """((0 + v0) + v1) + ... in the dtype of v."""
+    return np.add.accumulate(v)[-1]
 
 
 def compute_error(A, b, x):
-    """implicit.py:277-286 -- || b - A x ||_2."""
+    """implicit.py:277-286 -- sqrt(sum_i ||b_i - (A x)_i||^2), each term as norm()**2 = sqrt(.)^2."""
     r = b - _dense_matvec(A, x)
-    return np.sqrt((r * r).sum(dtype=A.dtype))
+    nrm = np.sqrt(_dot(r, r))
+    return np.sqrt(_seq_sum(nrm * nrm))
 
 
-def jacobi_iter_field(A, b, past_x, threshold=1e-5, max_iter=20000):
+def jacobi_iter_field_once(A, b, x, past_x):
+    """implicit.py:391-404 -- ONE serial in-place sweep (rows see already-updated x: Gauss-Seidel order)."""
+    ft = A.dtype.type
+    nv, dim = b.shape
+    omega = ft(0.75)
+    for i in range(nv):
+        t = _block_terms(A[i:i + 1], x)[0]                         # A[i,j] @ x[j] for every j, current x
+        bi = np.subtract.accumulate(np.concatenate([b[i][None], t]), axis=0)[-1]   # b -= ... , j ascending
+        for k in range(dim):
+            a_ii = A[i, i, k, k]
+            if abs(a_ii) < 1e-6:
+                x[i, k] = 0.0
+            else:
+                bk = bi[k] + a_ii * x[i, k]
+                x[i, k] = omega * bk / a_ii + (ft(1) - omega) * past_x[i, k]
+    return x
+
+
+def jacobi_iter_field(A, b, past_x, threshold=1e-5, max_iter=20000, trace=None):
     """implicit.py:227-262 + 391-404 -- the reference's 'Jacobi': a SERIAL
     in-place sweep (rows see already-updated x, i.e. Gauss-Seidel ordering),
     per-component diagonal solve, damped with omega=0.75 against past_vec_x,
     which is stale from the previous time step on the first iteration.
-    Returns (x, past_x, iterations)."""
+    Returns (x, past_x, iterations).  `trace` (a list) receives (err, x) per iteration."""
     ft = A.dtype.type
-    nv, dim = b.shape
-    omega = ft(0.75)
     x = ft(0.5) * b                                   # implicit.py:231-232
     err = compute_error(A, b, x)
     p_err = err
     it = 0
-    Aflat = A.transpose(0, 2, 1, 3).reshape(nv, dim, nv * dim)
+    past_x = past_x.copy()
     while err > threshold and it < max_iter:
-        xf = x.reshape(-1)
-        for i in range(nv):                           # implicit.py:393-404
-            bi = b[i] - Aflat[i] @ xf
-            for k in range(dim):
-                a_ii = A[i, i, k, k]
-                if abs(a_ii) < 1e-6:
-                    x[i, k] = 0.0
-                else:
-                    bk = bi[k] + a_ii * x[i, k]
-                    x[i, k] = omega * bk / a_ii + (ft(1) - omega) * past_x[i, k]
+        jacobi_iter_field_once(A, b, x, past_x)
         err = compute_error(A, b, x)
         it += 1
+        if trace is not None:
+            trace.append((float(err), x.copy()))
         if err >= p_err:                              # implicit.py:257-259
             x = past_x.copy()
             break
@@ -440,37 +481,44 @@ def jacobi_iter_field(A, b, past_x, threshold=1e-5, max_iter=20000):
     return x, past_x, it
 
 
-def cg(A, b, preconditioned, iter_max=500, tol=1e-5):
+def cg(A, b, preconditioned, iter_max=500, tol=1e-5, trace=None):
     """implicit.py:311-386 -- textbook CG on ATA x = ATb (preconditioned==1:
-    AT = A^T, implicit.py:289-299) or on A x = b (302-307); x0 = b; absolute
-    stop delta_new <= 1e-5; no residual refresh.  Returns (x, iterations, delta)."""
-    ft = A.dtype.type
+    AT[i,j] = A[j,i]^T, ATb, ATA built block by block, implicit.py:289-299) or on A x = b (302-307); x0 = b;
+    absolute stop delta_new <= 1e-5; no residual refresh.  Every sum runs in the reference's serial order.
+    Returns (x, iterations, delta)."""
     nv, dim = b.shape
-    M = A.transpose(0, 2, 1, 3).reshape(nv * dim, nv * dim)
-    bf = b.reshape(-1)
     if preconditioned == 1:
-        MT = M.T
-        ATb = MT @ bf
-        ATA = MT @ M
+        AT = A.transpose(1, 0, 3, 2).copy()
+        ATb = _dense_matvec(AT, b)                    # 0 + AT[i,0]@b[0] + ...
+        ATA = np.zeros_like(A)
+        for k in range(nv):                           # ATA[i,j] += AT[i,k] @ A[k,j], k ascending (296-299)
+            a, c = AT[:, k], A[k]                     # [nv,dim,dim] (i), [nv,dim,dim] (j)
+            blk = a[:, None, :, 0, None] * c[None, :, None, 0, :]
+            for m in range(1, dim):
+                blk = blk + a[:, None, :, m, None] * c[None, :, None, m, :]
+            ATA = ATA + blk
     else:
-        ATb = bf.copy()
-        ATA = M
-    x = bf.copy()
-    r = ATb - ATA @ x
+        ATb = b.copy()
+        ATA = A
+    x = b.copy()
+    # r[i] = ATb[i]; r[i] -= ATA[i,j] @ x[j], j ascending (324-327)
+    r = np.subtract.accumulate(np.concatenate([ATb[:, None], _block_terms(ATA, x)], axis=1), axis=1)[:, -1]
     d = r.copy()
-    delta_new = ft(r @ r)
+    delta_new = _seq_sum(_dot(r, r))
     it = 0
     while it < iter_max and delta_new > tol:
-        q = ATA @ d
-        alpha = delta_new / ft(d @ q)
+        q = _dense_matvec(ATA, d)
+        alpha = delta_new / _seq_sum(_dot(d, q))
         x = x + alpha * d
         r = r - alpha * q
         delta_old = delta_new
-        delta_new = ft(r @ r)
+        delta_new = _seq_sum(_dot(r, r))
         beta = delta_new / delta_old
         d = r + beta * d
         it += 1
-    return x.reshape(nv, dim), it, float(delta_new)
+        if trace is not None:
+            trace.append((float(delta_new), x.copy()))
+    return x, it, float(delta_new)
 
 
 def implicit_solver_neo_hookean(pos, vel, elems, ref, volume, mass, mu, s_lambda, dt,
@@ -492,10 +540,13 @@ def advect_implicit(pos, vel, vel_g, dt, g_dir, damping, blocks):
     zero vel_g, 420-423), blocks project v, vel, vel_g separately, pos += v dt."""
     ft = pos.dtype.type
     dim = pos.shape[1]
+    dt0 = dt
     dt = ft(dt)
     g = np.asarray(g_dir).astype(pos.dtype)
     vel_g += (ft(9.8) * g * dt)[None, :]
-    damp = np.exp(-dt * ft(damping))
+    # implicit.py:410-411: `ti.exp(-delta_time * obj.damping)` has only Python floats inside, so Taichi folds it in
+    # DOUBLE at compile time and rounds the factor to f32 (kinematic.py:23 differs: there dt, damping are f32 args)
+    damp = ft(math.exp(-float(dt0) * float(damping)))
     vel *= damp
     vel_g *= damp
     v = vel + vel_g
