@@ -4,6 +4,7 @@
 #include <cstdlib>
 #include <cstring>
 
+#include <omp.h>
 #include "object.h"
 
 using namespace femb;
@@ -202,6 +203,14 @@ int femb_object_destroy(femb_object* o) {
   for (void* p : o->allocs) cudaFree(p);
   if (o->h_sc) cudaFreeHost(o->h_sc);
   if (o->side) { cudaStreamSynchronize(o->side); cudaStreamDestroy(o->side); }
+  if (o->s_h2d) { cudaStreamSynchronize(o->s_h2d); cudaStreamDestroy(o->s_h2d); }
+  if (o->s_d2h) { cudaStreamSynchronize(o->s_d2h); cudaStreamDestroy(o->s_d2h); }
+  for (auto* arr : {o->xin, o->xout})
+    for (int i = 0; i < 48; ++i) {
+      if (arr[i].buf) cudaFree(arr[i].buf);
+      if (arr[i].copied) cudaEventDestroy(arr[i].copied);
+      if (arr[i].consumed) cudaEventDestroy(arr[i].consumed);
+    }
   if (o->ev_fork) cudaEventDestroy(o->ev_fork);
   if (o->ev_join) cudaEventDestroy(o->ev_join);
   if (o->own_stream && o->stream) cudaStreamDestroy(o->stream);
@@ -618,6 +627,83 @@ int femb_set(femb_object* o, int32_t field, const void* host, size_t bytes) {
   // the staging buffer is reused by the next call: make the copy-in complete before returning
   FEMB_CUDA(cudaStreamSynchronize(o->stream));
   FEMB_CATCH
+}
+
+// ---- asynchronous field transfers (pipelined host <-> device traffic) ------
+static femb_object::Xfer& xfer_slot(femb_object* o, femb_object::Xfer* arr, int field, size_t floats) {
+  if (field < 0 || field >= 48) throw ArgError("unknown field id");
+  femb_object::Xfer& x = arr[field];
+  if (!o->s_h2d) {
+    FEMB_CUDA(cudaStreamCreateWithFlags(&o->s_h2d, cudaStreamNonBlocking));
+    FEMB_CUDA(cudaStreamCreateWithFlags(&o->s_d2h, cudaStreamNonBlocking));
+  }
+  if (x.floats < floats) {
+    if (x.buf) { FEMB_CUDA(cudaDeviceSynchronize()); FEMB_CUDA(cudaFree(x.buf)); }
+    FEMB_CUDA(cudaMalloc(&x.buf, floats * sizeof(float)));
+    x.floats = floats;
+  }
+  if (!x.copied) {
+    FEMB_CUDA(cudaEventCreateWithFlags(&x.copied, cudaEventDisableTiming));
+    FEMB_CUDA(cudaEventCreateWithFlags(&x.consumed, cudaEventDisableTiming));
+  }
+  return x;
+}
+
+int femb_set_async(femb_object* o, int32_t field, const void* host, size_t bytes) {
+  FEMB_TRY
+  if (!o || !host) throw ArgError("femb_set_async: NULL argument");
+  FEMB_CUDA(cudaSetDevice(o->device));
+  const FieldRef r = resolve(o, field);
+  if (!r.vec) throw ArgError("femb_set_async: element fields are read-only");
+  if (field == FEMB_F_REF_POS) throw ArgError("femb_set_async: ref_pos is read-only");
+  if (bytes != r.count * sizeof(float)) throw ArgError("femb_set_async: byte count does not match the field size");
+  femb_object::Xfer& x = xfer_slot(o, o->xin, field, r.count);
+  // the previous unpack of this staging buffer must have read it before the next copy lands in it
+  if (x.used) FEMB_CUDA(cudaStreamWaitEvent(o->s_h2d, x.consumed, 0));
+  FEMB_CUDA(cudaMemcpyAsync(x.buf, host, bytes, cudaMemcpyHostToDevice, o->s_h2d));
+  FEMB_CUDA(cudaEventRecord(x.copied, o->s_h2d));
+  FEMB_CUDA(cudaStreamWaitEvent(o->stream, x.copied, 0));
+  launch_unpack_vertex(o->cfg, o->dim, o->n_vert, o->d_new_of_old, x.buf, r.comp0, r.ncomp, r.vec);
+  FEMB_CUDA(cudaEventRecord(x.consumed, o->stream));
+  x.used = true;
+  FEMB_CATCH
+}
+
+int femb_get_async(femb_object* o, int32_t field, void* host, size_t bytes) {
+  FEMB_TRY
+  if (!o || !host) throw ArgError("femb_get_async: NULL argument");
+  FEMB_CUDA(cudaSetDevice(o->device));
+  const FieldRef r = resolve(o, field);
+  if (bytes != r.count * sizeof(float)) throw ArgError("femb_get_async: byte count does not match the field size");
+  femb_object::Xfer& x = xfer_slot(o, o->xout, field, r.count);
+  // the previous device->host copy out of this staging buffer must have finished before it is packed again
+  if (x.used) FEMB_CUDA(cudaStreamWaitEvent(o->stream, x.copied, 0));
+  if (r.vec)
+    launch_pack_vertex(o->cfg, o->dim, o->n_vert, o->d_new_of_old, r.vec, r.comp0, r.ncomp, x.buf);
+  else
+    launch_pack_elem(o->cfg, o->dim, o->n_elem, o->d_slot_of_elem, o->e, o->h, o->d_phi, r.elem_what, x.buf);
+  FEMB_CUDA(cudaEventRecord(x.consumed, o->stream));
+  FEMB_CUDA(cudaStreamWaitEvent(o->s_d2h, x.consumed, 0));
+  FEMB_CUDA(cudaMemcpyAsync(host, x.buf, bytes, cudaMemcpyDeviceToHost, o->s_d2h));
+  FEMB_CUDA(cudaEventRecord(x.copied, o->s_d2h));
+  x.used = true;
+  FEMB_CATCH
+}
+
+int femb_transfers_wait(femb_object* o) {
+  FEMB_TRY
+  if (!o) throw ArgError("NULL object");
+  FEMB_CUDA(cudaSetDevice(o->device));
+  if (o->s_h2d) FEMB_CUDA(cudaStreamSynchronize(o->s_h2d));
+  FEMB_CUDA(cudaStreamSynchronize(o->stream));
+  if (o->s_d2h) FEMB_CUDA(cudaStreamSynchronize(o->s_d2h));
+  FEMB_CATCH
+}
+
+int femb_set_host_threads(int32_t n) {
+  // launchers such as torchrun export OMP_NUM_THREADS=1; the host-side tiling builder is OpenMP code
+  if (n > 0) omp_set_num_threads(n);
+  return omp_get_max_threads();
 }
 
 // ---- host-only tiling ------------------------------------------------------

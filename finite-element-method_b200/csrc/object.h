@@ -85,6 +85,17 @@ struct femb_object {
   int32_t* d_new_of_old = nullptr;
   int32_t* d_slot_of_elem = nullptr;
   float* d_stage = nullptr;         // marshalling buffer
+  // asynchronous field transfers (femb_set_async / femb_get_async): one staging buffer per field and direction,
+  // copies on two dedicated streams (PCIe is full duplex), ordered against the compute stream by events
+  struct Xfer {
+    float* buf = nullptr;
+    size_t floats = 0;
+    cudaEvent_t copied = nullptr;   // the PCIe copy of this buffer has finished
+    cudaEvent_t consumed = nullptr; // the unpack kernel has read it / the pack kernel may overwrite it
+    bool used = false;
+  };
+  Xfer xin[48], xout[48];
+  cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
   size_t stage_floats = 0;
   float4* d_blocks = nullptr;
   int n_blocks = 0, blocks_version = 0;

@@ -29,6 +29,7 @@ EXPORTS = [
     "femb_comm_bytes", "femb_peer_bind", "femb_peer_mass", "femb_reduce_bind", "femb_implicit_solve_begin", "femb_implicit_solve_advance", "femb_implicit_solve_poll",
     "femb_implicit_solve_finish",
     "femb_advect_implicit", "femb_implicit_assemble", "femb_implicit_apply", "femb_implicit_apply_timed", "femb_render", "femb_get", "femb_set",
+    "femb_set_async", "femb_get_async", "femb_transfers_wait", "femb_set_host_threads",
     "femb_get_energy", "femb_sync", "femb_last_error", "femb_launch_count", "femb_version",
     "femb_tiling_build", "femb_tiling_build_ex", "femb_tiling_destroy", "femb_tiling_info", "femb_tiling_get",
 ]
@@ -116,6 +117,10 @@ def lib():
         "femb_render": (C.c_int, [vp, C.POINTER(View), ip, i32, C.POINTER(C.c_uint8)]),
         "femb_get": (C.c_int, [vp, i32, vp, C.c_size_t]),
         "femb_set": (C.c_int, [vp, i32, vp, C.c_size_t]),
+        "femb_set_async": (C.c_int, [vp, i32, vp, C.c_size_t]),
+        "femb_get_async": (C.c_int, [vp, i32, vp, C.c_size_t]),
+        "femb_transfers_wait": (C.c_int, [vp]),
+        "femb_set_host_threads": (C.c_int, [i32]),
         "femb_get_energy": (C.c_int, [vp, fp]),
         "femb_sync": (C.c_int, [vp]),
         "femb_last_error": (C.c_char_p, []),
@@ -216,6 +221,21 @@ class Handle:
         if a.shape != self._shape(field):
             raise ValueError("field shape mismatch: %r vs %r" % (a.shape, self._shape(field)))
         check(lib().femb_set(self._h, field, a.ctypes.data_as(C.c_void_p), a.nbytes))
+
+    def set_async(self, field, arr):
+        """femb_set_async: `arr` (float32, C-contiguous, ideally page-locked) must stay alive until transfers_wait()."""
+        if arr.dtype != np.float32 or not arr.flags.c_contiguous or arr.shape != self._shape(field):
+            raise ValueError("set_async needs a C-contiguous float32 array of shape %r" % (self._shape(field),))
+        check(lib().femb_set_async(self._h, field, arr.ctypes.data_as(C.c_void_p), arr.nbytes))
+
+    def get_async(self, field, out):
+        if out.dtype != np.float32 or not out.flags.c_contiguous or out.shape != self._shape(field):
+            raise ValueError("get_async needs a C-contiguous float32 array of shape %r" % (self._shape(field),))
+        check(lib().femb_get_async(self._h, field, out.ctypes.data_as(C.c_void_p), out.nbytes))
+        return out
+
+    def transfers_wait(self):
+        check(lib().femb_transfers_wait(self._h))
 
     def info(self):
         i = Info()
@@ -364,6 +384,11 @@ def comm_bytes(max_halo):
     n, stride = C.c_size_t(), C.c_int32()
     check(lib().femb_comm_bytes(int(max_halo), C.byref(n), C.byref(stride)))
     return int(n.value), int(stride.value)
+
+
+def set_host_threads(n=0):
+    """OpenMP threads of the library's host-side set-up (0: only query)."""
+    return int(lib().femb_set_host_threads(int(n)))
 
 
 def launch_count():

@@ -9,6 +9,73 @@ redundantly -- no positions are ever exchanged, and a+b == b+a keeps both copies
 import numpy as np
 
 
+def rank_world():
+    """(rank, world) of this process: torch.distributed if it is initialised, else RANK / WORLD_SIZE from the
+    environment (torchrun), else (0, 1)."""
+    import os
+    try:
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized():
+            return dist.get_rank(), dist.get_world_size()
+    except ImportError:
+        pass
+    return int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+
+
+def ensure_process_group(backend=None):
+    """Under torchrun (WORLD_SIZE > 1) initialise the default process group once: NCCL with one GPU per rank
+    (LOCAL_RANK), gloo when no GPU is present (CPU tests).  Returns (rank, world)."""
+    import os
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        if not dist.is_initialized():
+            if backend is None:
+                backend = "nccl" if torch.cuda.is_available() else "gloo"
+            if backend == "nccl":
+                torch.cuda.set_device(local_device())
+                dist.init_process_group("nccl", device_id=torch.device("cuda", local_device()))
+            else:
+                dist.init_process_group(backend)
+    return rank_world()
+
+
+def local_device():
+    import os
+    return int(os.environ.get("LOCAL_RANK", "0"))
+
+
+def make_stream(handle):
+    """A non-default CUDA stream made current for torch and bound to the handle (the legacy default stream
+    cannot be graph-captured)."""
+    import torch
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+    handle.set_stream(stream.cuda_stream)
+    return stream
+
+
+def all_gather_arrays(arr):
+    """List of every rank's numpy array (different lengths allowed), on every rank."""
+    import torch
+    import torch.distributed as dist
+    world = dist.get_world_size()
+    dev = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend() == "nccl" else torch.device("cpu")
+    a = np.ascontiguousarray(arr)
+    n = torch.tensor([a.shape[0]], dtype=torch.int64, device=dev)
+    sizes = [torch.zeros_like(n) for _ in range(world)]
+    dist.all_gather(sizes, n)
+    sizes = [int(s.item()) for s in sizes]
+    t = torch.zeros((max(sizes),) + a.shape[1:], dtype=torch.from_numpy(a).dtype, device=dev)
+    t[:a.shape[0]] = torch.from_numpy(a).to(dev)
+    outs = [torch.empty_like(t) for _ in range(world)]
+    dist.all_gather(outs, t)
+    if dev.type == "cuda":
+        torch.cuda.current_stream().synchronize()
+    return [o[:k].cpu().numpy() for o, k in zip(outs, sizes)]
+
+
 def slab_range(n_layers, rank, world):
     """Cell layers [i0, i1) of `rank` when `n_layers` x-layers are dealt to `world` ranks."""
     base, rem = divmod(n_layers, world)

@@ -12,16 +12,31 @@ class VertexField:
         if grad_field is not None:
             self.grad = VertexField(obj, grad_field)
 
-    def to_numpy(self):
+    def to_numpy(self, out=None, blocking=True):
+        """Taichi's field.to_numpy().  Extensions: `out` (a float32 array, page-locked for speed) receives the copy;
+        blocking=False only enqueues it (device->host copy stream) -- call obj.sync() before reading `out`."""
         if self._field == _capi.F_FORCE:
             self._obj._materialize_force()
-        return self._obj._h.get(self._field)
+        if not blocking:
+            if out is None:
+                raise ValueError("to_numpy(blocking=False) needs out=")
+            return self._obj._h.get_async(self._field, out)
+        return self._obj._h.get(self._field, out=out)
 
-    def from_numpy(self, arr):
+    def from_numpy(self, arr, blocking=True):
+        """Taichi's field.from_numpy().  Extension: blocking=False enqueues the copy on the host->device copy stream
+        (it overlaps the kernels of earlier calls); `arr` must stay untouched until obj.sync()."""
         if not self._writable:
             raise RuntimeError("field is read-only")
-        if self._field == _capi.F_FORCE:
+        if not blocking:
             self._obj._materialize_force()
+            if self._field == _capi.F_FORCE:
+                self._obj._force_clean = False
+            return self._obj._h.set_async(self._field, arr)
+        # a requested-but-deferred neo_hookean_1_grad must see the state of ITS call time (explicit.py:8): run it
+        # before any vertex field changes under it
+        self._obj._materialize_force()
+        if self._field == _capi.F_FORCE:
             self._obj._force_clean = False
         self._obj._h.set(self._field, arr)
 

@@ -88,6 +88,12 @@ if __name__ == '__main__':
     args = parser.parse_args()
     config = utils.read_config(args.config)
     utils.sys_init(config)
+    # extension: under torchrun (one process per GPU) structured 3D boxes are cut into x-slabs by object.Object
+    from femb200 import dist as fdist
+    rank, world = fdist.ensure_process_group()
+    if world > 1:
+        from femb200 import _capi
+        _capi.set_host_threads(max(1, (os.cpu_count() or 1) // world))   # torchrun exports OMP_NUM_THREADS=1
 
     import constants
     from render.render import Render
@@ -99,7 +105,7 @@ if __name__ == '__main__':
     from circle_blocks import CircleBlocks
 
     os.makedirs(args.out, exist_ok=True)
-    render = None if args.no_render else Render(config, output_dir=args.out)
+    render = None if (args.no_render or rank != 0 and world > 1) else Render(config, output_dir=args.out)
     sim_count = config.get('sim_count')
     circle_blocks = CircleBlocks(config.get('blocks'))
     soft_objects = [Object(i) for i in config.get('objects')]
@@ -143,11 +149,14 @@ if __name__ == '__main__':
         o.sync()
     wall = time.perf_counter() - t0
     n_elem = sum(o.element_cnt for o in soft_objects)
-    print('{} frames x {} steps, {} elements: {:.3f} s wall, {:.3e} element-updates/s'.format(
-        args.frames, sim_count, n_elem, wall, args.frames * sim_count * n_elem / max(wall, 1e-9)))
+    print('{} frames x {} steps, {} elements{}: {:.3f} s wall, {:.3e} element-updates/s'.format(
+        args.frames, sim_count, n_elem, ' on this rank of {} rank(s)'.format(world) if world > 1 else '', wall,
+        args.frames * sim_count * n_elem / max(wall, 1e-9)))
     if render is not None:
         render.finish()
     if args.checkpoint:
         save_checkpoint(args.checkpoint, soft_objects, frame0 + args.frames, virtual_time)
         print('checkpoint written to {}'.format(args.checkpoint))
     sys.stdout.flush()
+    if world > 1:
+        fdist.shutdown()

@@ -13,6 +13,16 @@ Mesh sources (config dict of one entry of "objects"):
             "side_length" + "subdivisions", no "obj" (extension, SURVEY.md 8 f1: the 2D keys in 3D --
                                                       a Kuhn cube of subdivisions^3 cells)
   any dim : Object.from_arrays(config, vertices, elements)   (extension: bring your own mesh)
+
+Multi-GPU (extension; the reference is single-device, main.py:40): when the process runs under
+torch.distributed with WORLD_SIZE > 1 (one process per GPU, `torchrun main.py ...`), a STRUCTURED 3D config
+("cells"+"h" or "side_length"+"subdivisions") is cut into x-slabs of cell layers by Object itself: this rank
+builds and owns only its slab, binds the peer-memory halo exchange (femb200.dist.SlabHalo) and the solver calls
+(neo_hookean_1_grad + kinematic, implicit_solver_neo_hookean, advect_implicit) work unchanged -- the halo sums
+and the dot-product sums happen inside the library's kernels.  Fields are LOCAL to the rank
+(`particles.pos.to_numpy()` returns this slab, shared interface planes included on both owners);
+`obj.gather(obj.particles.pos)` assembles the global array on every rank.  Unstructured meshes are far too small
+to shard: every rank then simply holds a replica.
 """
 import numpy as np
 
@@ -22,8 +32,11 @@ from femb200 import _capi, fields, meshgen
 
 class Object:
 
-    def __init__(self, config, vertices=None, elements=None, faces=None, tile_elems=0, device=-1):
+    def __init__(self, config, vertices=None, elements=None, faces=None, tile_elems=0, device=-1, partition=True):
         dim = constants.dim
+        self._slab = None            # (rank, world, i0, i1, (nx, ny, nz)) when this object is one x-slab of a box
+        self._halo = None
+        self._partition = partition
         self.rho = config.get("rho")
         E, nu = config.get('E'), config.get('nu')
         self.mu, self.s_lambda = E / 2 / (1 + nu), E * nu / (1 + nu) / (1 - 2 * nu)   # object.py:47-48
@@ -42,8 +55,19 @@ class Object:
         self.element_cnt = elements.shape[0]
         # the reference allocates the linear-system vectors only for the implicit path (object.py:78-93)
         self.implicit = not constants.use_explicit_method
+        halo_kw = {}
+        if self._slab is not None:
+            from femb200 import dist as fdist
+            rank, world, i0, i1, (nx, ny, nz) = self._slab
+            self._halo = fdist.SlabHalo(rank, world, i1 - i0, ny, nz)
+            halo_kw = dict(halo_verts=self._halo.vertex_ids, halo_owned=self._halo.owned)
+            device = fdist.local_device() if device < 0 else device
         self._h = _capi.Handle(vertices, elements, self.center, self.rho, self.mu, self.s_lambda, self.damping,
-                               implicit=self.implicit, tile_elems=tile_elems, device=device)
+                               implicit=self.implicit, tile_elems=tile_elems, device=device, **halo_kw)
+        if self._halo is not None:
+            # graph capture needs a real stream (the legacy default stream cannot be captured)
+            self._stream = fdist.make_stream(self._h)
+            self._halo.attach(self._h, mode=config.get('comm'))
         self.particles = fields.Particles(self)
         self.elements = fields.Elements(self, elements)
         self.meshs = fields.Meshs(self, np.asarray(faces, dtype=np.int32))
@@ -62,7 +86,13 @@ class Object:
         if config.get('jitter'):
             rng = np.random.default_rng(config.get('seed', 0))
             h = config.get('h') or (config.get('side_length', 1.0) / max(config.get('subdivisions', 1), 1))
-            jit = rng.uniform(-1.0, 1.0, vertices.shape).astype(np.float32)
+            if self._slab is None:
+                jit = rng.uniform(-1.0, 1.0, vertices.shape).astype(np.float32)
+            else:
+                # drawn for the GLOBAL vertex array so that both owners of a shared plane see the same values
+                _, _, i0, i1, (nx, ny, nz) = self._slab
+                plane = (ny + 1) * (nz + 1)
+                jit = rng.uniform(-1.0, 1.0, ((nx + 1) * plane, 3)).astype(np.float32)[i0 * plane:(i1 + 1) * plane]
             pos = (vertices + self.center[None, :].astype(np.float32)).astype(np.float32)
             self._h.set(_capi.F_POS, pos + np.float32(config.get('jitter') * h) * jit)
         self._pending_grad = False   # neo_hookean_1_grad requested, not yet materialised
@@ -88,17 +118,46 @@ class Object:
         if constants.dim == 2:
             return self.construct_2d_mesh(config)
         self.center = np.asarray(config.get('center'), dtype=np.float32)
+        box = None
         if config.get('cells') is not None:
-            nx, ny, nz = config.get('cells')
-            vertices, elements = meshgen.kuhn_box(nx, ny, nz, config.get('h'))
+            box = tuple(int(c) for c in config.get('cells')) + (float(config.get('h')),)
         elif config.get('obj') is None and config.get('side_length') and config.get('subdivisions'):
             n = int(config.get('subdivisions'))
-            vertices, elements = meshgen.kuhn_box(n, n, n, config.get('side_length') / n)
+            box = (n, n, n, config.get('side_length') / n)
+        if box is not None:
+            nx, ny, nz, h = box
+            from femb200 import dist as fdist
+            rank, world = fdist.rank_world() if self._partition else (0, 1)
+            if world > 1:
+                if nx < world:
+                    raise ValueError("cannot cut %d cell layers into %d slabs" % (nx, world))
+                i0, i1 = fdist.slab_range(nx, rank, world)
+                self._slab = (rank, world, i0, i1, (nx, ny, nz))
+                vertices, elements = meshgen.kuhn_box(nx, ny, nz, h, x_cells=(i0, i1))
+            else:
+                vertices, elements = meshgen.kuhn_box(nx, ny, nz, h)
         else:
             from femb200 import meshio
             vertices, elements, self.surface_source = meshio.tetrahedralize_file(config.get('obj'))
-        faces = meshgen.boundary_faces(vertices, elements)
+        if config.get('surface', True):
+            faces = meshgen.boundary_faces(vertices, elements)
+            if self._slab is not None:
+                faces = self._drop_interface_faces(faces)
+        else:                       # extension: skip the surface of huge benchmark meshes ("surface": false)
+            faces = np.zeros((0, 3), np.int32)
         return vertices, faces, elements
+
+    def _drop_interface_faces(self, faces):
+        """Faces of a slab that lie in a plane shared with a neighbour rank are interior faces of the box."""
+        rank, world, i0, i1, (nx, ny, nz) = self._slab
+        plane = (ny + 1) * (nz + 1)
+        layer = faces // plane
+        keep = np.ones(len(faces), bool)
+        if rank > 0:
+            keep &= ~(layer == 0).all(axis=1)
+        if rank < world - 1:
+            keep &= ~(layer == (i1 - i0)).all(axis=1)
+        return faces[keep]
 
     # -- helpers used by the solver wrappers ---------------------------------
     def _sync_blocks(self, circle_blocks):
@@ -109,9 +168,44 @@ class Object:
 
     def _materialize_force(self):
         if self._pending_grad:
+            if self._halo is not None:
+                raise RuntimeError("on a slab-partitioned object the gradient exists only inside the fused step "
+                                   "(neo_hookean_1_grad followed by kinematic): particles.force cannot be read or "
+                                   "the state rewritten in between")
             self._h.explicit_grad()
             self._pending_grad = False
             self._force_clean = False
+
+    # -- the calls the solver wrappers make (single GPU: the handle; slab: the handle + its halo exchange)
+    def _explicit_step(self, dt, g_dir, n=1):
+        if self._halo is not None:
+            self._halo.explicit_steps(self._h, dt, g_dir, n)
+        else:
+            self._h.explicit_step(dt, g_dir, n)
+
+    def _implicit_solve(self, dt, method, preconditioned, **kw):
+        if self._halo is not None:
+            return self._halo.implicit_solve(self._h, dt, method, preconditioned, **kw)
+        return self._h.implicit_solve(dt, method, preconditioned, **kw)
+
+    @property
+    def global_particle_cnt(self):
+        if self._slab is None:
+            return self.particle_cnt
+        _, _, _, _, (nx, ny, nz) = self._slab
+        return (nx + 1) * (ny + 1) * (nz + 1)
+
+    def gather(self, field):
+        """Global [Nv, dim] array of a vertex field on EVERY rank (slab objects; a no-op copy otherwise).  Shared
+        interface planes are bit-identical on both owners; the left owner's copy is taken."""
+        local = field.to_numpy()
+        if self._slab is None:
+            return local
+        from femb200 import dist as fdist
+        rank, world, i0, i1, (nx, ny, nz) = self._slab
+        plane = (ny + 1) * (nz + 1)
+        parts = fdist.all_gather_arrays(local if rank == world - 1 else local[:(i1 - i0) * plane])
+        return np.concatenate(parts, axis=0)
 
     # -- output (object.py:322-335) -----------------------------------------
     def update_obj(self):
@@ -144,4 +238,6 @@ class Object:
         return int((dets(pos) * dets(ref) <= 0).sum())
 
     def sync(self):
+        """Wait for every enqueued kernel and (non-blocking) field transfer of this object."""
+        self._h.transfers_wait()
         self._h.sync()

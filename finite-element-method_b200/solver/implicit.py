@@ -6,8 +6,8 @@ import constants
 
 
 def implicit_solver_neo_hookean(obj):
-    it, resid = obj._h.implicit_solve(constants.delta_time, constants.implicit_method,
-                                      1 if constants.preconditioned == 1 else 0)
+    it, resid = obj._implicit_solve(constants.delta_time, constants.implicit_method,
+                                    1 if constants.preconditioned == 1 else 0)
     obj.last_solve = {"iters": it, "resid": resid}
 
 

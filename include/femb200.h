@@ -210,6 +210,15 @@ int femb_render(femb_object *obj, const femb_view *view, const int32_t *prims, i
 /* ---- field access: field.to_numpy() / field.from_numpy() */
 int femb_get(femb_object *obj, int32_t field, void *host, size_t bytes);
 int femb_set(femb_object *obj, int32_t field, const void *host, size_t bytes);
+/* Asynchronous variants for pipelined host traffic (new; the reference's to_numpy/from_numpy, object.py:62-67,
+ * render.py:67, are synchronous copies).  `host` should be page-locked and must stay valid until
+ * femb_transfers_wait() (or femb_sync after it) returns.  femb_set_async copies on a dedicated H2D stream and orders
+ * the scatter into the field BEFORE any later call on the object; femb_get_async packs the field AFTER all earlier
+ * calls and copies on a dedicated D2H stream -- so H2D of step k+1, the kernels of step k and D2H of step k-1
+ * overlap (PCIe is full duplex).  One staging buffer per field and direction: re-use is ordered by events. */
+int femb_set_async(femb_object *obj, int32_t field, const void *host, size_t bytes);
+int femb_get_async(femb_object *obj, int32_t field, void *host, size_t bytes);
+int femb_transfers_wait(femb_object *obj);
 /* obj.U[None] (object.py:69) */
 int femb_get_energy(femb_object *obj, float *U_out);
 int femb_sync(femb_object *obj);
@@ -219,6 +228,9 @@ const char *femb_last_error(void);
 /* number of CUDA kernels this library has launched in this process */
 uint64_t femb_launch_count(void);
 const char *femb_version(void);
+
+/* OpenMP threads of the host-side set-up code (tiling builder); returns the count in effect.  n <= 0 only queries. */
+int femb_set_host_threads(int32_t n);
 
 /* ---- host-only tiling (no CUDA calls): used by tests to check the layout invariants */
 int femb_tiling_build(int32_t dim, int32_t n_vert, int32_t n_elem, const float *verts,

@@ -19,6 +19,7 @@ def lib():
         _lib = C.CDLL(_PATH)
         _lib.fem_ref_threads.restype = C.c_int
         _lib.fem_ref_cg.restype = C.c_int
+        _lib.fem_ref_jacobi.restype = C.c_int
     return _lib
 
 
@@ -32,6 +33,24 @@ def _i(a):
 
 def threads():
     return lib().fem_ref_threads()
+
+
+def set_threads(n=None):
+    """Use `n` (default: every host core) OpenMP threads, whatever OMP_NUM_THREADS the launcher exported
+    (torchrun sets it to 1)."""
+    lib().fem_ref_set_threads(C.c_int(int(n or os.cpu_count() or 1)))
+    return threads()
+
+
+def elements_init(pos, elems, rho):
+    """object.py:345-362 in C: (ref, volume, mass); mass by atomic adds (order differs from the serial oracle)."""
+    nv, d = pos.shape
+    ref = np.empty((len(elems), d, d), dtype=np.float32)
+    vol = np.empty(len(elems), dtype=np.float32)
+    mass = np.empty(nv, dtype=np.float32)
+    lib().fem_ref_elements_init(C.c_int(d), C.c_int64(nv), C.c_int64(len(elems)), _i(elems), _f(pos), C.c_float(rho),
+                                _f(ref), _f(vol), _f(mass))
+    return ref, vol, mass
 
 
 def _blocks(blocks, d):
@@ -83,3 +102,14 @@ def cg(H, elems, mass, dt, b, preconditioned, iter_max=500, tol=1e-5):
                           C.c_int(int(preconditioned)), _f(b), _f(x), C.c_int(iter_max), C.c_float(tol), _f(work),
                           C.byref(delta))
     return x, it, delta.value
+
+
+def jacobi(H, elems, mass, dt, b, past_x, iter_max=20000, tol=1e-5):
+    """Simultaneous weighted Jacobi with the matrix-free operator (timing baseline; see fem_ref.c)."""
+    nv, d = b.shape
+    x = np.empty_like(b)
+    work = np.empty(4 * nv * d, dtype=np.float32)
+    err = C.c_float()
+    it = lib().fem_ref_jacobi(C.c_int(d), C.c_int64(nv), C.c_int64(len(elems)), _i(elems), _f(H), _f(mass), C.c_float(dt),
+                              _f(b), _f(x), _f(past_x), C.c_int(iter_max), C.c_float(tol), _f(work), C.byref(err))
+    return x, it, err.value

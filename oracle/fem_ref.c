@@ -262,3 +262,96 @@ int fem_ref_cg(int d, int64_t nv, int64_t ne, const int32_t* elems, const float*
   if (delta_out) *delta_out = delta_new;
   return it;
 }
+
+/* bench.py sets the thread count itself: launchers such as torchrun export OMP_NUM_THREADS=1 */
+void fem_ref_set_threads(int n) { if (n > 0) omp_set_num_threads(n); }
+
+/* object.py:345-362, 375-392 : Dm^-1, volume, lumped mass (atomic adds) */
+void fem_ref_elements_init(int d, int64_t nv, int64_t ne, const int32_t* elems, const float* pos, float rho,
+                           float* ref, float* vol, float* mass) {
+  memset(mass, 0, (size_t)nv * sizeof(float));
+  const float share = (float)(1.0 / (d + 1));
+#pragma omp parallel for schedule(static)
+  for (int64_t e = 0; e < ne; ++e) {
+    const int32_t* el = elems + e * (d + 1);
+    float X[MAXD][MAXD], R[MAXD][MAXD];
+    const float* p0 = pos + (size_t)el[0] * d;
+    for (int j = 0; j < d; ++j) {
+      const float* pj = pos + (size_t)el[j + 1] * d;
+      for (int i = 0; i < d; ++i) X[i][j] = pj[i] - p0[i];
+    }
+    float V;
+    if (d == 2) {
+      V = fabsf(X[0][0] * X[1][1] - X[1][0] * X[0][1]) / 2.0f;
+    } else {
+      const float cx = X[1][1] * X[2][2] - X[2][1] * X[1][2];
+      const float cy = X[2][1] * X[0][2] - X[0][1] * X[2][2];
+      const float cz = X[0][1] * X[1][2] - X[1][1] * X[0][2];
+      V = (float)(1.0 / 6.0) * fabsf(X[0][0] * cx + X[1][0] * cy + X[2][0] * cz);
+    }
+    vol[e] = V;
+    const float m = share * V * rho;
+    for (int j = 0; j <= d; ++j) {
+#pragma omp atomic
+      mass[el[j]] += m;
+    }
+    inv_m(d, X, R);
+    for (int i = 0; i < d; ++i)
+      for (int j = 0; j < d; ++j) ref[(size_t)e * d * d + i * d + j] = R[i][j];
+  }
+}
+
+/* diag(A)_{v,k} = 1 - dt^2/m_v * sum_e c_{e,v} H_e[k][k]  (c = d for local vertex 0, else 1) */
+void fem_ref_diag(int d, int64_t nv, int64_t ne, const int32_t* elems, const float* H, const float* mass, float dt,
+                  float* diag) {
+  memset(diag, 0, (size_t)nv * d * sizeof(float));
+#pragma omp parallel for schedule(static)
+  for (int64_t e = 0; e < ne; ++e) {
+    const int32_t* el = elems + e * (d + 1);
+    for (int j = 0; j <= d; ++j)
+      for (int k = 0; k < d; ++k) {
+        const float c = (j == 0 ? (float)d : 1.0f) * H[(size_t)e * d * d + k * d + k];
+#pragma omp atomic
+        diag[(size_t)el[j] * d + k] += c;
+      }
+  }
+#pragma omp parallel for schedule(static)
+  for (int64_t v = 0; v < nv; ++v)
+    for (int k = 0; k < d; ++k) diag[v * d + k] = 1.0f - dt * dt * (1.0f / mass[v]) * diag[v * d + k];
+}
+
+/* Weighted Jacobi iterations with the matrix-free operator (the loop of implicit.py:227-262 with the sweep of
+ * 391-404 evaluated simultaneously -- a timing baseline for "one operator pass + update + residual norm" per
+ * iteration; the reference's own sweep is serial and dense).  work: 4*nv*d floats.  Returns iterations. */
+int fem_ref_jacobi(int d, int64_t nv, int64_t ne, const int32_t* elems, const float* H, const float* mass, float dt,
+                   const float* b, float* x, float* past_x, int iter_max, float tol, float* work, float* err_out) {
+  const int64_t n = nv * d;
+  float *ax = work, *diag = work + n, *scr = work + 2 * n;
+  fem_ref_diag(d, nv, ne, elems, H, mass, dt, diag);
+#pragma omp parallel for schedule(static)
+  for (int64_t i = 0; i < n; ++i) x[i] = 0.5f * b[i];
+  fem_ref_apply(d, nv, ne, elems, H, mass, dt, 0, x, ax, scr);
+  double s = 0.0;
+#pragma omp parallel for reduction(+ : s) schedule(static)
+  for (int64_t i = 0; i < n; ++i) s += (double)(b[i] - ax[i]) * (b[i] - ax[i]);
+  float err = (float)sqrt(s), p_err = err;
+  int it = 0;
+  while (err > tol && it < iter_max) {
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < n; ++i) {
+      const float a = diag[i];
+      x[i] = fabsf(a) < 1e-6f ? 0.f : 0.75f * (b[i] - ax[i] + a * x[i]) / a + 0.25f * past_x[i];
+    }
+    fem_ref_apply(d, nv, ne, elems, H, mass, dt, 0, x, ax, scr);
+    s = 0.0;
+#pragma omp parallel for reduction(+ : s) schedule(static)
+    for (int64_t i = 0; i < n; ++i) s += (double)(b[i] - ax[i]) * (b[i] - ax[i]);
+    err = (float)sqrt(s);
+    ++it;
+    if (tol > 0.f && err >= p_err) { memcpy(x, past_x, n * sizeof(float)); break; }
+    p_err = err;
+    memcpy(past_x, x, n * sizeof(float));
+  }
+  if (err_out) *err_out = err;
+  return it;
+}

@@ -180,3 +180,32 @@ def test_two_rank_slabs_match_single_gpu(comm, extra):
                         os.path.join(ROOT, "tests", "mp_slab_check.py")], capture_output=True, text=True, timeout=180,
                        env=env)
     assert "SLAB_OK" in r.stdout and ("COMM " + comm) in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+@pytest.mark.gpu
+def test_public_api_on_two_ranks_matches_single_gpu():
+    """object.Object cuts the box into slabs under torchrun; neo_hookean_1_grad / kinematic /
+    implicit_solver_neo_hookean / advect_implicit run unchanged (main.py:101-113) and match the 1-GPU run."""
+    import torch
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29613",
+                        os.path.join(ROOT, "tests", "mp_public_api_check.py")], capture_output=True, text=True, timeout=300)
+    assert "PUBLIC_SLAB_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+@pytest.mark.gpu
+def test_main_py_under_torchrun(tmp_path):
+    """`torchrun --nproc-per-node 2 main.py --config config/cube_1m.json --frames 2`: the driver runs on 2 GPUs with no new calls."""
+    import torch
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    pkg = os.path.join(ROOT, "finite-element-method_b200")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29615", os.path.join(pkg, "main.py"),
+                        "--config", os.path.join(pkg, "config", "cube_1m.json"), "--frames", "2", "--no-render",
+                        "--out", str(tmp_path)], capture_output=True, text=True, timeout=300, cwd=pkg)
+    assert r.returncode == 0 and "element-updates/s" in r.stdout and "2 rank(s)" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
