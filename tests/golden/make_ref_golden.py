@@ -52,6 +52,13 @@ def kuhn_cube(n, side):
     return verts.astype(np.float64), np.asarray(tets, np.int32)
 
 
+def asset_mesh(name):
+    sys.path.insert(0, os.path.join(ROOT, "finite-element-method_b200"))
+    from femb200 import meshio
+    nodes, tets, _ = meshio.tetrahedralize_file(os.path.join(ROOT, "finite-element-method_b200", "obj", name))
+    return nodes.astype(np.float64), tets.astype(np.int32)
+
+
 def cfg2d(**kw):
     c = copy.deepcopy(DEFAULT)
     obj = kw.pop("obj", {})
@@ -116,6 +123,16 @@ def cases():
     C["k3_walls_cg"] = (cfg3d(implicit_method=1, preconditioned=0, obj=walls, **imp), k3, dict(stretch=0.05, jitter=0.008, seed=3, rand_vel=0.5), 40, (1, 10, 20, 40))
     C["k3_cg_stiff"] = (cfg3d(implicit_method=1, preconditioned=0, delta_time=4e-3, obj=cube, blocks=blk3, **imp), k3, st3, 10, (1, 2, 5, 10), True)
     C["k3_cg_ata_stiff"] = (cfg3d(implicit_method=1, preconditioned=1, delta_time=4e-3, obj=cube, blocks=blk3, **imp), k3, st3, 4, (1, 2, 4), True)
+    # BASELINE configs 2 and 5 on the assets they name (config/demo_3d.json:2-28 with the edits SURVEY.md 8 lists).
+    # TetGen is not installable: the tet mesh comes from the product's fallback mesher (femb200.meshio) and the SAME
+    # arrays are stored in the fixture and fed to every side.
+    spot100, spot = asset_mesh("spot100.obj"), asset_mesh("spot.obj")
+    sts = dict(stretch=0.05, jitter=0.002, seed=4)
+    C["spot100_cg"] = (cfg3d(implicit_method=1, preconditioned=0, **imp), spot100, sts, 100, rec100)
+    C["spot100_cg_ata"] = (cfg3d(implicit_method=1, preconditioned=1, **imp), spot100, sts, 3, (1, 2, 3))
+    C["spot100_jacobi"] = (cfg3d(implicit_method=0, **imp), spot100, sts, 30, (1, 2, 10, 30))
+    C["spot_analytic"] = (cfg3d(), spot, sts, 100, rec100)
+    C["spot_autodiff"] = (cfg3d(auto_diff=True), spot, sts, 20, (1, 2, 10, 20))
     # stiff Jacobi (dt 4x): the serial in-place sweep vs a simultaneous Jacobi part ways here
     C["s5_jacobi_stiff"] = (cfg2d(implicit_method=0, delta_time=2e-3, obj=sq(5), **imp), None, st2, 6, (1, 2, 3, 6), True)
     return C
