@@ -153,6 +153,23 @@ int femb_object_create(const femb_desc* d, femb_object** out) {
                        t.n_slots, (t.max_tile_elems + 31) / 32 * 32, t.max_lv, (t.max_rounds + 3) / 4 * 4, t.nc,
                        prop.multiProcessorCount * occ, grid, t.n_halo_tiles, d_bskip};
 
+    // in-tile completion of boundary vertices (tile_pass.cuh: itc_arrive): arrival counters armed with -(slots);
+    // vertices shared with another rank get a count that is never reached (the halo boundary kernel owns them)
+    // Measured (profiles/r02_ab_itc.log): correct, but SLOWER -- C4 explicit 0.274 -> 0.355 ms, C3 22.7 -> 27.1 us: the
+    // fence -> atomic -> dependent loads chain sits at the end of every tile CTA's life and idles its SM slot.
+    // Off unless FEMB_ITC=1.
+    const char* itc_env = std::getenv("FEMB_ITC");
+    if (t.n_boundary > 0 && itc_env && itc_env[0] == '1') {
+      std::vector<int32_t> cnt((size_t)t.n_boundary);
+      for (int b = 0; b < t.n_boundary; ++b) cnt[b] = t.bptr[b] - t.bptr[b + 1];
+      for (int32_t b : t.halo_b) cnt[b] = -(1 << 30);
+      int32_t* d_cnt;
+      upload(d_cnt, cnt);
+      o->dtl.bcount = d_cnt;
+      o->dtl.halo_b = o->halo.b;
+      o->dtl.n_halo_b = o->halo.n;
+    }
+
     const size_t ns = (size_t)t.n_slots, nv = (size_t)t.n_vert;
     o->e.p0 = o->alloc<float4>(ns);
     o->e.p1 = o->alloc<float4>(ns);
@@ -610,6 +627,7 @@ int femb_get(femb_object* o, int32_t field, void* host, size_t bytes) {
     launch_pack_elem(o->cfg, o->dim, o->n_elem, o->d_slot_of_elem, o->e, o->h, o->d_phi, r.elem_what, o->d_stage);
   FEMB_CUDA(cudaMemcpyAsync(host, o->d_stage, bytes, cudaMemcpyDeviceToHost, o->stream));
   FEMB_CUDA(cudaStreamSynchronize(o->stream));
+  o->check_comm_error();   // a peer wait that timed out must not hand out stale data silently
   FEMB_CATCH
 }
 

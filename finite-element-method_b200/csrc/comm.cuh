@@ -69,14 +69,18 @@ __device__ __forceinline__ void halo_send_cta(const PeerComm& pc, int n, const i
 
 // Receive side inside a consumer kernel: every CTA waits for both neighbours' flags (begin) and the last CTA to
 // finish advances the sequence (end).  Returns the parity of the receive plane to read.
-__device__ __forceinline__ uint32_t halo_recv_begin(const PeerComm& pc, uint32_t& seq) {
+// `need`: this thread will read a received value.  Only CTAs that own a shared vertex wait for the neighbours'
+// flags -- the (many) CTAs of ordinary boundary vertices never see the NVLink latency.
+__device__ __forceinline__ uint32_t halo_recv_begin(const PeerComm& pc, uint32_t& seq, bool need = true) {
   CommState* st = pc.st;
   seq = st->recv_seq + 1;
-  if (threadIdx.x == 0) {
-    if (pc.left) spin_until(&hdr_of(pc.self)->halo_flag[0], seq, st);
-    if (pc.right) spin_until(&hdr_of(pc.self)->halo_flag[1], seq, st);
+  if (__syncthreads_or(need ? 1 : 0)) {
+    if (threadIdx.x == 0) {
+      if (pc.left) spin_until(&hdr_of(pc.self)->halo_flag[0], seq, st);
+      if (pc.right) spin_until(&hdr_of(pc.self)->halo_flag[1], seq, st);
+    }
+    __syncthreads();
   }
-  __syncthreads();
   return seq & 1u;
 }
 __device__ __forceinline__ void halo_recv_end(const PeerComm& pc, uint32_t seq) {

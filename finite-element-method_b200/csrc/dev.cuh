@@ -51,6 +51,10 @@ struct DevTiling {
   const HaloDev* hd;     // nullptr: no exchange in this launch
   int n_send;            // tile kernel: its first n_send CTAs send the halo sums of the (finished) halo tiles
   int fuse_recv;         // boundary kernel: wait for the neighbours and add their sums itself
+  // in-tile completion of boundary vertices (tile_pass.cuh: itc_arrive); nullptr = off (FEMB_ITC=0)
+  int32_t* bcount;       // [n_boundary] arrival counters, armed with -(partial slots); shared-with-a-rank: never reached
+  const int32_t* halo_b; // [n_halo_b] boundary indices of the vertices shared with another rank
+  int n_halo_b;
 };
 
 // Shared-memory layout of k_tile (byte offsets; every region is 16-byte aligned):

@@ -75,6 +75,7 @@ struct OpSetup {
     Material mat;
   };
   __device__ static bool early_exit(const Args&) { return false; }
+  __host__ __device__ static bool itc(const Args&) { return true; }
   __device__ static float w0() { return 1.f; }
   __device__ static float4* partial_buf(const Args& a) { return a.vs.partial; }
   __device__ static double* red_buf(const Args&) { return nullptr; }
@@ -166,6 +167,7 @@ struct OpExplicit {
     double* red;
   };
   __device__ static bool early_exit(const Args&) { return false; }
+  __host__ __device__ static bool itc(const Args&) { return !REDUCE; }
   __device__ static float w0() { return 0.f; }
   __device__ static float4* partial_buf(const Args& a) { return a.vs.partial; }
   __device__ static double* red_buf(const Args& a) { return a.red; }

@@ -29,6 +29,7 @@ struct OpAssemble {
     ImplicitVecs iv;
   };
   __device__ static bool early_exit(const Args&) { return false; }
+  __host__ __device__ static bool itc(const Args&) { return true; }
   __device__ static float w0() { return 0.f; }
   __device__ static float4* partial_buf(const Args& a) { return a.vs.partial; }
   __device__ static double* red_buf(const Args&) { return nullptr; }
@@ -126,6 +127,7 @@ struct OpDiag {
     ImplicitVecs iv;
   };
   __device__ static bool early_exit(const Args&) { return false; }
+  __host__ __device__ static bool itc(const Args&) { return true; }
   __device__ static float w0() { return (float)D; }
   __device__ static float4* partial_buf(const Args& a) { return a.vs.partial; }
   __device__ static double* red_buf(const Args&) { return nullptr; }
@@ -172,6 +174,7 @@ struct OpApply {
     const SolveScalars* sc;
   };
   __device__ static bool early_exit(const Args& a) { return a.sc && (a.sc->done | a.sc->terminal); }
+  __host__ __device__ static bool itc(const Args& a) { return a.epilogue == AP_PLAIN; }   // reductions keep k_boundary
   __device__ static float w0() { return 0.f; }
   __device__ static float4* partial_buf(const Args& a) { return a.partial; }
   __device__ static double* red_buf(const Args& a) { return a.red; }

@@ -159,6 +159,46 @@ __device__ __forceinline__ void gather_local_vertex(int n_rounds, const uint32_t
   }
 }
 
+// In-tile completion (ITC) of boundary vertices.  Every boundary vertex b carries an arrival counter armed with
+// -(number of partial slots).  A tile CTA that has stored its partial sum of b makes it visible (fence) and bumps
+// the counter; the CTA whose bump finds -1 is the LAST of the tiles that touch b: it re-arms the counter, sums the
+// slots IN SLOT ORDER (so the result does not depend on who arrived last -- bit-identical to k_boundary) and
+// finishes the vertex with Op::vertex.  By then every touching tile has read the vertex's operands (they are
+// staged at tile start), so writing its new state is safe; no other tile reads it.  The boundary kernel, its
+// launch and its tail disappear; vertices shared with another RANK are armed with a count that is never reached
+// and stay with the (tiny) halo boundary kernel, which also receives the neighbour's sums.
+// Ops that accumulate a reduction in Op::vertex keep k_boundary (the split of the sum over CTAs would depend on
+// arrival order); Op::itc(args) says which launches qualify.
+template <int D, class Op>
+__device__ __forceinline__ void itc_arrive(const DevTiling& tl, const typename Op::Args& a, int gid, const float4& vtx,
+                                           float& red) {
+  __threadfence();                                   // my partial slot is visible before the counter moves
+  const int b = gid - tl.n_interior;
+  if (atomicAdd(tl.bcount + b, 1) != -1) return;
+  __threadfence();                                   // the other tiles' slots are visible after it has moved
+  const int s0 = tl.bptr[b], s1 = tl.bptr[b + 1];
+  tl.bcount[b] = s0 - s1;                            // re-armed for the next pass
+  const float4* part = Op::partial_buf(a);
+  const float4 pre = Op::pre(a, gid);
+  float acc[D];
+#pragma unroll
+  for (int i = 0; i < D; ++i) acc[i] = 0.f;
+  for (int s = s0; s < s1; s += 4) {                 // same order of adds as k_boundary
+    float4 p[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) p[k] = s + k < s1 ? __ldcg(part + s + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      if (s + k < s1) {
+        acc[0] += p[k].x;
+        acc[1] += p[k].y;
+        if (D == 3) acc[D - 1] += p[k].z;
+      }
+    }
+  }
+  Op::vertex(a, gid, vtx, pre, acc, red);
+}
+
 // Persistent form: CTA c owns tiles c, c+G, c+2G, ...  While it works on tile t it already has, in flight or
 // landed, everything its next tile t' = t+G needs to start without a dependent global round trip:
 //   iteration start : TMA {descriptor, local-vertex table} of t' -> second buffer; TMA {JDS lists} of t;
@@ -180,6 +220,7 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile_persistent(Dev
     return;
   }
   if (Op::early_exit(a)) return;
+  const bool itc = tl.bcount != nullptr && Op::itc(a);
   const int bid = (int)blockIdx.x - n_send;
   int t = t_begin + bid;
   if (t >= t_end) return;
@@ -307,6 +348,7 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile_persistent(Dev
         float4 p;
         p.x = acc[0]; p.y = acc[1]; p.z = D == 3 ? acc[D - 1] : 0.f; p.w = 0.f;
         Op::partial_buf(a)[v.part] = p;
+        if (itc) itc_arrive<D, Op>(tl, a, v.gid, sv[l], red);
       }
     }
     if (!has_next) break;
@@ -335,6 +377,7 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile(DevTiling tl, 
     return;
   }
   if (Op::early_exit(a)) return;
+  const bool itc = tl.bcount != nullptr && Op::itc(a);
   const int bid = (int)blockIdx.x - n_send;
   const int tile = t_begin + bid;
   const DevTile td = tl.tiles[tile];
@@ -413,6 +456,7 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile(DevTiling tl, 
       float4 p;
       p.x = acc[0]; p.y = acc[1]; p.z = D == 3 ? acc[D - 1] : 0.f; p.w = 0.f;
       Op::partial_buf(a)[v.part] = p;
+      if (itc) itc_arrive<D, Op>(tl, a, v.gid, sv[l], red);
     }
   }
   if (Op::REDUCE) {
@@ -426,20 +470,24 @@ constexpr int kBoundaryBlock = 256;
 
 // FUSE: multi-GPU launches whose halo exchange is received here (the single-GPU instantiation carries none of it)
 template <int D, class Op, bool FUSE>
-__global__ void __launch_bounds__(kBoundaryBlock) k_boundary(DevTiling tl, typename Op::Args a, int red_base) {
+__global__ void __launch_bounds__(kBoundaryBlock) k_boundary(DevTiling tl, typename Op::Args a, int red_base,
+                                                             const int32_t* list, int n_list) {
   __shared__ float s_warp[32];
   // multi-GPU, exchange fused into this kernel: the neighbours' sums of the shared vertices are read straight
   // from the receive plane they stored into (no unpack kernel).  The sequence bookkeeping runs even when the
   // solver has already converged, so that all ranks keep counting the same exchanges.
   const HaloDev* hd = FUSE ? tl.hd : nullptr;
   uint32_t rseq = 0, rparity = 0;
-  if (hd) rparity = halo_recv_begin(hd->pc, rseq);
+  // list != nullptr: only these boundary vertices (the ones shared with another rank -- every other boundary vertex
+  // was finished inside the tile kernel, see itc_arrive); their arrival counters are re-armed by their huge count
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const int b = list ? (idx < n_list ? list[idx] : tl.n_boundary) : idx;
+  if (hd) rparity = halo_recv_begin(hd->pc, rseq, b < tl.n_boundary && hd->bhalo[b] >= 0);
   if (Op::early_exit(a)) {
     if (hd) halo_recv_end(hd->pc, rseq);
     return;
   }
   float red = 0.f;
-  const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b < tl.n_boundary) {
     const float4* part = Op::partial_buf(a);
     const int hk = FUSE ? hd->bhalo[b] : -1;        // >= 0: shared vertex, its last slot is the remote one
@@ -558,9 +606,13 @@ inline void run_tile_pass(const char* name, const LaunchCfg& c, const DevTiling&
     }
   }
   if (c.ev_mid) cudaEventRecord(c.ev_mid, c.stream);
-  if (tl.n_boundary > 0 && c.phase != 1) {
+  const bool itc = tl.bcount != nullptr && Op::itc(a);
+  const int32_t* list = itc ? tl.halo_b : nullptr;
+  const int n_list = itc ? tl.n_halo_b : 0;
+  const int n_bnd = itc ? n_list : tl.n_boundary;
+  if (n_bnd > 0 && c.phase != 1) {
     tl.fuse_recv = c.hd ? c.fuse_recv : 0;
-    const int nb = (tl.n_boundary + kBoundaryBlock - 1) / kBoundaryBlock;
+    const int nb = (n_bnd + kBoundaryBlock - 1) / kBoundaryBlock;
 #if FEMB_PDL
     // programmatic dependent launch: the boundary kernel's CTAs are scheduled while the tile kernel drains
     cudaLaunchConfig_t lc = {};
@@ -573,12 +625,12 @@ inline void run_tile_pass(const char* name, const LaunchCfg& c, const DevTiling&
     at[0].val.programmaticStreamSerializationAllowed = 1;
     lc.attrs = at;
     lc.numAttrs = 1;
-    cudaLaunchKernelEx(&lc, k_boundary<D, Op, false>, tl, a, tile_grid<Op>(tl, split, persist));
+    cudaLaunchKernelEx(&lc, k_boundary<D, Op, false>, tl, a, tile_grid<Op>(tl, split, persist), list, n_list);
 #else
     if (tl.fuse_recv && tl.hd)
-      k_boundary<D, Op, true><<<nb, kBoundaryBlock, 0, c.stream>>>(tl, a, tile_grid<Op>(tl, split, persist));
+      k_boundary<D, Op, true><<<nb, kBoundaryBlock, 0, c.stream>>>(tl, a, tile_grid<Op>(tl, split, persist), list, n_list);
     else
-      k_boundary<D, Op, false><<<nb, kBoundaryBlock, 0, c.stream>>>(tl, a, tile_grid<Op>(tl, split, persist));
+      k_boundary<D, Op, false><<<nb, kBoundaryBlock, 0, c.stream>>>(tl, a, tile_grid<Op>(tl, split, persist), list, n_list);
 #endif
     note_launch(name, c.stream);
   }

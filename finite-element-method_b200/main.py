@@ -41,8 +41,9 @@ def step(soft_obj, circle_blocks):
         advect_implicit(soft_obj, circle_blocks)
 
 
-def save_checkpoint(path, soft_objects, frame, virtual_time):
-    data = {"frame": frame, "virtual_time": virtual_time, "n_objects": len(soft_objects)}
+def save_checkpoint(path, soft_objects, frame, virtual_time, ply_cnt=0, output_frame_cnt=0):
+    data = {"frame": frame, "virtual_time": virtual_time, "n_objects": len(soft_objects), "ply_cnt": ply_cnt,
+            "output_frame_cnt": output_frame_cnt}
     for k, o in enumerate(soft_objects):
         data["pos%d" % k] = o.particles.pos.to_numpy()
         data["vel%d" % k] = o.particles.vel.to_numpy()
@@ -62,7 +63,8 @@ def load_checkpoint(path, soft_objects):
         if o.implicit and ("vel_g%d" % k) in z:
             o.particles.vel_g.from_numpy(z["vel_g%d" % k])
             o.past_vec_x.from_numpy(z["past_x%d" % k])
-    return int(z["frame"]), float(z["virtual_time"])
+    counters = (int(z["ply_cnt"]) if "ply_cnt" in z else None, int(z["output_frame_cnt"]) if "output_frame_cnt" in z else None)
+    return int(z["frame"]), float(z["virtual_time"]), counters
 
 
 def diagnostics(soft_obj):
@@ -118,8 +120,11 @@ if __name__ == '__main__':
     ply_cnt = 0
     frame0 = 0
     if args.resume:
-        frame0, virtual_time = load_checkpoint(args.resume, soft_objects)
-        ply_cnt = int(virtual_time / frame_time)
+        frame0, virtual_time, (ck_ply, ck_out) = load_checkpoint(args.resume, soft_objects)
+        # the export counters continue where the checkpointed run stopped (no frame is written twice)
+        ply_cnt = ck_ply if ck_ply is not None else int(virtual_time / frame_time) + 1
+        if render is not None and ck_out is not None:
+            render.output_frame_cnt = ck_out
     if constants.use_explicit_method:
         print('Simulation method: explicit method. Auto-diff {}'.format(bool(constants.auto_diff)))
     elif constants.implicit_method == constants.JACOBIN_METHOD:
@@ -138,10 +143,14 @@ if __name__ == '__main__':
             if virtual_time / frame_time > ply_cnt:
                 if is_output_obj and constants.dim == 3:
                     soft_obj.update_obj()
-                    soft_obj.save_obj(os.path.join(args.out, '{:06d}.obj'.format(ply_cnt)))
+                    soft_obj.save_obj(os.path.join(args.out, 'obj_{:06d}.obj'.format(ply_cnt)))   # main.py:121 name
                 ply_cnt += 1
         if render is not None:
-            render.render(soft_objects, circle_blocks, virtual_time)
+            msgs = []
+            if not render.is_output_gif:                 # main.py:124-127
+                msgs.append("frame_cnt: {}".format(frame_cnt + 1))
+                msgs.append("time: {:.4f}".format(virtual_time))
+            render.render(soft_objects, circle_blocks, virtual_time, msgs)
         if args.diag_every and (frame_cnt + 1) % args.diag_every == 0:
             for k, o in enumerate(soft_objects):
                 print('frame {} object {}: {}'.format(frame_cnt + 1, k, json.dumps(diagnostics(o))))
@@ -155,7 +164,8 @@ if __name__ == '__main__':
     if render is not None:
         render.finish()
     if args.checkpoint:
-        save_checkpoint(args.checkpoint, soft_objects, frame0 + args.frames, virtual_time)
+        save_checkpoint(args.checkpoint, soft_objects, frame0 + args.frames, virtual_time, ply_cnt,
+                        render.output_frame_cnt if render is not None else 0)
         print('checkpoint written to {}'.format(args.checkpoint))
     sys.stdout.flush()
     if world > 1:

@@ -70,7 +70,11 @@ class Render:
         self.frames = []            # uint8 [H, W, 3] images kept for the video
         self.last_image = None
         self.rendered = 0
-        self.keep_state = config.get('keep_state', True)  # positions (+ phi in 2D) per frame -> frames.npz
+        # positions (+ phi in 2D) per frame -> frames.npz.  Default: on for small scenes only (a 16 M-tet box would
+        # copy 32 MB to the host and keep it, every frame); `keep_state` in the config overrides
+        self.keep_state = config.get('keep_state', None)
+        self.keep_state_max_vertices = 200000
+        self.max_frames = int(config.get('max_frames', 2000))   # frames kept in memory for the GIF
         self.states = []
 
     # -- one frame ------------------------------------------------------------------------------
@@ -97,16 +101,21 @@ class Render:
         """render.py:110-117: every call draws (the reference shows the window each frame); the frame goes
         to the video only when virtual time has passed the next 1/output_fps mark (render.py:77 / :101)."""
         img = self.image(soft_objects, circle_blocks)
+        if msgs:
+            img = draw_text(img, msgs)       # gui.text(msg) overlay, render.py:108-111 (frame count / time)
         self.last_image = img
         self.rendered += 1
-        if self.keep_state:
+        keep_state = self.keep_state
+        if keep_state is None:
+            keep_state = sum(getattr(o, "particle_cnt", 0) for o in soft_objects) <= self.keep_state_max_vertices
+        if keep_state:
             st = {'pos': np.concatenate([o.particles.pos.to_numpy() for o in soft_objects])}
             if constants.dim == 2:
                 st['phi'] = np.concatenate([o.phi.to_numpy() for o in soft_objects])
             self.states.append(st)
         due = virtual_time is None or (virtual_time / self.frame_time) > self.output_frame_cnt
         if due and (self.keep_frames or self.save_png):
-            if self.keep_frames:
+            if self.keep_frames and len(self.frames) < self.max_frames:
                 self.frames.append(img)
             if self.save_png:
                 from PIL import Image
@@ -134,3 +143,16 @@ class Render:
             ims[0].save(path, save_all=True, append_images=ims[1:], duration=max(1, int(round(1000.0 / self.output_fps))),
                         loop=0)
         return path
+
+
+def draw_text(img, msgs, origin=(6, 6), color=(255, 255, 255)):
+    """The reference's `gui.text(msg, pos)` overlay (render/render.py:108-111: one line per message from the top
+    left): PIL's built-in bitmap font blitted on the host into the finished frame -- no graphics stack involved."""
+    from PIL import Image, ImageDraw
+    im = Image.fromarray(img)
+    d = ImageDraw.Draw(im)
+    x, y = origin
+    for m in msgs:
+        d.text((x, y), str(m), fill=tuple(color))
+        y += 14
+    return np.asarray(im).copy()

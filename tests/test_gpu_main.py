@@ -55,7 +55,7 @@ def test_every_mode_runs_and_stays_finite(tmp_path, base, edits, banner):
     assert frames["pos"][-1][:, 1].mean() < frames["pos"][0][:, 1].mean()
     if edits.get("is_output_obj"):
         objs = sorted(f for f in os.listdir(out) if f.endswith(".obj"))
-        assert objs and objs[0] == "000000.obj"
+        assert objs and objs[0] == "obj_000000.obj"
         lines = open(out / objs[0]).read().splitlines()
         assert sum(l.startswith("v ") for l in lines) > 100 and sum(l.startswith("f ") for l in lines) > 100
 

@@ -66,9 +66,10 @@ def test_checkpoint_roundtrip_and_mismatch(main_mod, tmp_path):
     m, _, _ = main_mod
     objs = [_Obj(5, False, 1), _Obj(7, True, 2)]
     path = str(tmp_path / "ck.npz")
-    m.save_checkpoint(path, objs, 42, 0.21)
+    m.save_checkpoint(path, objs, 42, 0.21, ply_cnt=13, output_frame_cnt=12)
     fresh = [_Obj(5, False, 11), _Obj(7, True, 12)]
-    frame, vt = m.load_checkpoint(path, fresh)
+    frame, vt, counters = m.load_checkpoint(path, fresh)
+    assert counters == (13, 12)
     assert (frame, vt) == (42, 0.21)
     for a, b in zip(objs, fresh):
         assert np.array_equal(a.particles.pos.a, b.particles.pos.a) and np.array_equal(a.particles.vel.a, b.particles.vel.a)

@@ -97,3 +97,13 @@ def test_no_gif_config_and_3d_camera_arguments(tmp_path):
     r.finish()
     assert sorted(os.listdir(tmp_path)) == ["frames.npz", "last.png"]
     assert Render({"is_output_gif": False}, output_dir=str(tmp_path / "none")).finish() is None
+
+
+def test_text_overlay_draws_the_messages():
+    """render/render.py:108-111: gui.text(msg) per message, top left."""
+    from render.render import draw_text
+    img = np.zeros((64, 200, 3), np.uint8)
+    out = draw_text(img, ["frame_cnt: 7", "time: 0.0350"])
+    assert out.shape == img.shape and out.dtype == np.uint8
+    assert out[:34].any() and not out[40:].any()          # two text lines near the top, nothing below
+    assert not img.any()                                   # the input frame is not modified
