@@ -192,6 +192,8 @@ int femb_object_create(const femb_desc* d, femb_object** out) {
       float4** vecs[] = {&o->iv.b, &o->iv.x, &o->iv.past_x, &o->iv.d, &o->iv.r,
                          &o->iv.q, &o->iv.atb, &o->iv.tmp, &o->iv.diag};
       for (float4** p : vecs) *p = o->alloc<float4>(nv);
+      o->iv.w = o->alloc<float4>(nv);
+      o->d_red2 = o->alloc<double>((size_t)o->red_slots);
       o->d_sc = o->alloc<SolveScalars>(1);
       FEMB_CUDA(cudaMallocHost(&o->h_sc, sizeof(SolveScalars)));
     }

@@ -108,6 +108,25 @@ struct Builder {
     add([ob, n_red] { launch_reduce_final(ob->cfg, n_red, ob->d_red, ob->d_allred); }, FEMB_COMM_ALLREDUCE);
     add([ob, consume] { consume(1, ob->d_allred, PeerComm{}); });
   }
+
+  // two global sums consumed by ONE scalar kernel (single-reduction CG): partials red_a[0..n_a), red_b[0..n_b)
+  using Sum2Fn = std::function<void(int, const double*, int, const double*, const PeerComm&)>;
+  void gsum2(int n_a, const double* red_a, int n_b, const double* red_b, Sum2Fn consume) {
+    femb_object* ob = o;
+    if (!dist) {
+      add([=] { consume(n_a, red_a, n_b, red_b, PeerComm{}); });
+      return;
+    }
+    if (ob->peer_on) {   // the scalar kernel sums locally, scatters, gathers (twice) and does the math
+      add([=] { consume(n_a, red_a, n_b, red_b, ob->peer); });
+      return;
+    }
+    add([=] {            // caller-side collective: both local sums into the bound buffer, ONE all-reduce
+      launch_reduce_final(ob->cfg, n_a, red_a, ob->d_allred);
+      launch_reduce_final(ob->cfg, n_b, red_b, ob->d_allred + 1);
+    }, FEMB_COMM_ALLREDUCE);
+    add([=] { consume(1, ob->d_allred, 1, ob->d_allred + 1, PeerComm{}); });
+  }
 };
 
 void build_program(femb_object* o, SolveProgram& P, float dt, int method, int preconditioned, int max_iter, float tol) {
@@ -118,6 +137,7 @@ void build_program(femb_object* o, SolveProgram& P, float dt, int method, int pr
   if (tol < 0.f) tol = 1e-5f;                          // implicit.py:236,341
   if (max_iter <= 0) max_iter = method == 1 ? 500 : 20000;  // implicit.py:337,237
   P.method = method;
+  P.pre = preconditioned == 1 ? 1 : 0;
   o->last_method = method;
   P.max_iter = max_iter;
   const float ktol = P.fixed ? -1.f : tol;
@@ -151,26 +171,36 @@ void build_program(femb_object* o, SolveProgram& P, float dt, int method, int pr
     } else {
       pro.pass(apply(0, iv.b, iv.q, AP_PLAIN, nullptr, nullptr, nullptr), kApplyPersist);
     }
-    pro.add([=] { launch_cg_init(o->cfg, nv, iv, rhs, iv.q, o->d_red, mask); });   // x = b, r = rhs - op(x), d = r
+    const int cgcg = preconditioned == 1 ? 1 : 0;   // A^T A: single-reduction CG (OpCgFirst); plain A: the textbook loop
+    pro.add([=] { launch_cg_init_ex(o->cfg, nv, iv, rhs, iv.q, o->d_red, mask, cgcg); });   // x = b, r = rhs - op(x), d = r
     pro.gsum(vred, [=](int n, const double* red, const PeerComm& pc) { launch_cg_delta0(o->cfg, n, red, sc, ktol, max_iter, pc); });
 
-    if (preconditioned == 1) {
-      it.pass(apply(0, iv.d, iv.tmp, AP_PLAIN, nullptr, nullptr, sc), kApplyPersist);
-      it.pass(apply(1, iv.tmp, iv.q, AP_DOT, iv.d, nullptr, sc), kApplyPersist);
+    if (cgcg) {
+      // iteration = [pending update + tmp = A r, partials of r.r] [w = A^T tmp, partials of r.w] [scalars]
+      it.pass([o, dim, dt, sc](const LaunchCfg& c) {
+        launch_cgcg_first(dim, c, o->dtl, o->h, o->vs, dt, o->iv, o->d_red2, sc);
+      }, kApplyPersist);
+      it.pass(apply(1, iv.tmp, iv.w, AP_DOT, iv.r, nullptr, sc), kApplyPersist);
+      it.gsum2(ared, o->d_red2, ared, o->d_red,
+               [=](int na, const double* ra, int nb, const double* rb, const PeerComm& pc) {
+                 launch_cgcg_scalar(o->cfg, na, ra, nb, rb, sc, ktol, max_iter, pc);
+               });
     } else {
       it.pass(apply(0, iv.d, iv.q, AP_DOT, iv.d, nullptr, sc), kApplyPersist);
+      it.gsum(ared, [=](int n, const double* red, const PeerComm& pc) { launch_cg_alpha(o->cfg, n, red, sc, pc); });
+      it.add([=] { launch_cg_update_xr(o->cfg, nv, iv, o->d_red, sc, mask); });
+      it.gsum(vred, [=](int n, const double* red, const PeerComm& pc) { launch_cg_beta(o->cfg, n, red, sc, ktol, max_iter, pc); });
+      it.add([=] { launch_cg_update_d(o->cfg, nv, iv, sc); });
     }
-    it.gsum(ared, [=](int n, const double* red, const PeerComm& pc) { launch_cg_alpha(o->cfg, n, red, sc, pc); });
-    it.add([=] { launch_cg_update_xr(o->cfg, nv, iv, o->d_red, sc, mask); });
-    it.gsum(vred, [=](int n, const double* red, const PeerComm& pc) { launch_cg_beta(o->cfg, n, red, sc, ktol, max_iter, pc); });
-    it.add([=] { launch_cg_update_d(o->cfg, nv, iv, sc); });
   } else {
     // ---- the reference's damped "Jacobi" (227-262, 391-404) as a true parallel Jacobi
     pro.pass([o, dim, dt](const LaunchCfg& c) { launch_implicit_diag(dim, c, o->dtl, o->h, o->vs, dt, o->iv); });
     pro.add([=] { launch_scale_xyz(o->cfg, nv, iv.b, iv.x, 0.5f); });               // x0 = 0.5 b (231-232)
-    it.pass(apply(0, iv.x, iv.tmp, AP_RESID, iv.b, iv.r, sc), kApplyPersist);
+    // one fused pass per iteration (residual norm + the next iterate, kernels_implicit.cu: OpJacobi) + the decision
+    it.pass([o, dim, dt, sc](const LaunchCfg& c) {
+      launch_jacobi_pass(dim, c, o->dtl, o->h, o->vs, dt, o->iv, o->d_red, sc);
+    }, kApplyPersist);
     it.gsum(ared, [=](int n, const double* red, const PeerComm& pc) { launch_jacobi_decide(o->cfg, n, red, sc, tol, max_iter, fixed, pc); });
-    it.add([=] { launch_jacobi_update(o->cfg, nv, iv, sc); });
   }
 }
 
@@ -196,6 +226,8 @@ void check_solve_args(femb_object* o, int method) {
 }
 
 void finish(femb_object* o, int32_t* iters_out, float* resid_out) {
+  if (o->prog->method == 0) launch_jacobi_finish(o->cfg, o->n_vert, o->iv, o->d_sc);   // answer buffer -> vec_x, past_vec_x
+  if (o->prog->method == 1 && o->prog->pre) launch_cgcg_finish(o->cfg, o->n_vert, o->iv, o->d_sc);   // a scheduled, unapplied update
   launch_copy_xyz(o->cfg, o->n_vert, o->iv.x, o->vs.vel);          // vel = x (222-223)
   if (iters_out || resid_out) {
     poll(o);
@@ -278,7 +310,8 @@ int femb_implicit_solve(femb_object* o, float dt, int32_t method, int32_t precon
   build_program(o, P, dt, method, preconditioned, max_iter, tol);
   advance(o);                                          // prologue (no communication on one GPU)
   // Jacobi needs one more residual evaluation than updates, plus the pass that sets `done`
-  const int n_it = method == 1 ? P.max_iter : P.max_iter + 2;
+  // single-reduction CG evaluates r.r of the iterate of update k in iteration k + 1: one more pass to see the last one
+  const int n_it = method == 1 ? P.max_iter + ((P.pre && !P.fixed) ? 1 : 0) : P.max_iter + 2;
   // one iteration (all its kernels, peer-memory communication included) as a CUDA graph: the argument
   // values of an iteration never change, so the graph is cached per (dt, method, tolerance ...)
   SolveGraph& g = o->solve_graph;

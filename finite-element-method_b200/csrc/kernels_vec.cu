@@ -71,7 +71,7 @@ __global__ void k_scalars_reset(SolveScalars* sc) {
 
 // x = b ; r = rhs - op(x) ; d = r ; partial r.r        (implicit.py:313-334)
 __global__ void __launch_bounds__(256) k_cg_init(int n, ImplicitVecs iv, const float4* rhs, const float4* opx,
-                                                 double* red, RedMask mask) {
+                                                 double* red, RedMask mask, int zero_ps) {
   __shared__ float s_warp[32];
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   float v = 0.f;
@@ -80,7 +80,12 @@ __global__ void __launch_bounds__(256) k_cg_init(int n, ImplicitVecs iv, const f
     const float4 r = make_float4(a.x - o.x, a.y - o.y, a.z - o.z, 0.f);
     iv.x[i] = b;
     iv.r[i] = r;
-    iv.d[i] = r;
+    if (zero_ps) {   // single-reduction CG: p_{-1} = s_{-1} = 0 (the first update has beta = 0, but 0 * stale inf = NaN)
+      iv.d[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+      iv.q[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    } else {
+      iv.d[i] = r;
+    }
     v = counted(mask, i) ? dot3(r, r) : 0.f;
   }
   const float t = block_sum(v, s_warp);
@@ -109,6 +114,56 @@ __global__ void __launch_bounds__(kFinalThreads) k_cg_scalar(int kind, int n_red
     sc->iters += 1;
     sc->done = !(sc->iters < max_iter && (tol < 0.f || (float)s > tol));
   }
+}
+
+// Single-reduction CG: gamma = r.r (partials of the first pass), delta = r.w (partials of the A^T pass).
+// Loop test of implicit.py:341 on the EXACT gamma of the current residual, then alpha / beta of the update the
+// next first pass will apply (Chronopoulos-Gear recurrences; identical to delta_new / d.q in exact arithmetic).
+__global__ void __launch_bounds__(kFinalThreads) k_cgcg_scalar(int n_g, const double* red_g, int n_d, const double* red_d,
+                                                              SolveScalars* sc, float tol, int max_iter, PeerComm pc) {
+  if (pc.st == nullptr && sc->done) return;
+  const double g = global_sum(red_g, n_g, pc);
+  __syncthreads();                                       // final_sum's shared scratch is reused
+  const double dl = global_sum(red_d, n_d, pc);
+  if (sc->done) return;
+  if (threadIdx.x != 0) return;
+  sc->delta_old = sc->delta_new;
+  sc->delta_new = g;
+  sc->dq = dl;
+  const bool go = sc->iters < max_iter && (tol < 0.f || (float)g > tol);
+  if (!go) {
+    sc->done = 1;
+    sc->pending = 0;
+    return;
+  }
+  float alpha, beta;
+  if (!sc->pending) {                                    // first iteration of the solve: p = r, s = w
+    beta = 0.f;
+    alpha = (float)g / (float)dl;
+  } else {
+    beta = (float)g / (float)sc->gamma_old;
+    alpha = (float)g / ((float)dl - beta * (float)g / sc->alpha);
+  }
+  sc->alpha = alpha;
+  sc->beta = beta;
+  sc->gamma_old = g;
+  sc->iters += 1;
+  sc->pending = 1;
+}
+
+// end of a single-reduction CG solve: an update that was scheduled but never applied (fixed iteration count, or the
+// caller's iteration budget ran out) is applied to x here
+__global__ void __launch_bounds__(256) k_cgcg_finish(int n, ImplicitVecs iv, const SolveScalars* sc) {
+  if (!sc->pending) return;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float alpha = sc->alpha, beta = sc->beta;
+  const float4 r = iv.r[i], p0 = iv.d[i];
+  float4 x = iv.x[i];
+  x.x += alpha * (r.x + beta * p0.x);
+  x.y += alpha * (r.y + beta * p0.y);
+  x.z += alpha * (r.z + beta * p0.z);
+  iv.x[i] = x;
 }
 
 // x += alpha d ; r -= alpha q ; partial r.r               (implicit.py:357-381)
@@ -145,7 +200,12 @@ __global__ void __launch_bounds__(256) k_cg_update_d(int n, ImplicitVecs iv, con
   iv.d[i] = d;
 }
 
-// Jacobi control flow, implicit.py:234-261, from err = ||b - A x|| of the CURRENT iterate.
+// Jacobi control flow, implicit.py:234-261, from err = ||b - A x_k|| of the iterate the pass just evaluated (x_k sits
+// in buffer sc->cur; the pass has also written the candidate x_{k+1} into the next buffer, see OpJacobi).
+//   continue : iters += 1, cur advances -- the next pass evaluates x_{k+1}
+//   stop     : terminal; the answer is x_k (ans = cur); past_vec_x := x_k unless no iterate was ever accepted
+//   revert   : terminal; the answer is x_{k-1} (the buffer before cur), or past_vec_x ITSELF when the very first
+//              sweep made things worse (the reference then restores the STALE vector of the previous time step)
 __global__ void __launch_bounds__(kFinalThreads) k_jacobi_decide(int n_red, const double* red, SolveScalars* sc, float tol,
                                                        int max_iter, int fixed, PeerComm pc) {
   if (pc.st == nullptr && sc->done) return;
@@ -157,66 +217,56 @@ __global__ void __launch_bounds__(kFinalThreads) k_jacobi_decide(int n_red, cons
   }
   if (threadIdx.x != 0) return;
   const float err = sqrtf((float)s);
-  int action = JA_NONE;
+  const int cur = sc->cur, nxt = cur == 2 ? 0 : cur + 1, prv = cur == 0 ? 2 : cur - 1;
   sc->err = err;
   if (fixed) {                 // benchmark mode: exactly max_iter updates, no revert / early stop
     sc->p_err = err;
     sc->first = 0;
     if (sc->iters < max_iter) {
       sc->iters += 1;
-      sc->action = JA_ACCEPT | JA_UPDATE;
+      sc->cur = nxt;
     } else {
       sc->terminal = 1;
-      sc->action = JA_ACCEPT;
+      sc->ans = cur;
+      sc->keep_past = 0;
     }
     return;
   }
+  bool revert = false;
   if (sc->first) {
     sc->p_err = err;           // p_err = err (235); past_vec_x stays stale
     sc->first = 0;
+    sc->keep_past = 1;         // nothing cached yet
   } else if (err >= (float)sc->p_err) {
-    action = JA_REVERT;        // recover_past_frame_x ; break (257-259)
+    revert = true;             // recover_past_frame_x ; break (257-259)
     sc->terminal = 1;
+    // keep_past still set: x_{k-1} = x_0 was never cached -> the answer is the stale past_vec_x, left as it is;
+    // otherwise past_vec_x holds x_{k-1} (cached when it was accepted) = the answer
+    sc->ans = sc->keep_past ? 3 : prv;
   } else {
     sc->p_err = err;           // p_err = err ; cache_x (260-261)
-    action = JA_ACCEPT;
+    sc->keep_past = 0;
   }
-  if (action != JA_REVERT) {
+  if (!revert) {
     if (err > tol && sc->iters < max_iter) {   // while condition (252)
-      action |= JA_UPDATE;
       sc->iters += 1;
+      sc->cur = nxt;
     } else {
       sc->terminal = 1;
+      sc->ans = cur;
     }
   }
-  sc->action = action;
 }
 
-// cache_x / recover / one damped Jacobi update (implicit.py:266-274, 391-404)
-__global__ void __launch_bounds__(256) k_jacobi_update(int n, ImplicitVecs iv, const SolveScalars* sc) {
-  if (sc->done) return;
-  const int action = sc->action;
+// end of the solve: vec_x = the answer, past_vec_x = what the reference's cache_x / recover left there
+__global__ void __launch_bounds__(256) k_jacobi_finish(int n, ImplicitVecs iv, const SolveScalars* sc) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n || action == JA_NONE) return;
-  if (action & JA_REVERT) {
-    iv.x[i] = iv.past_x[i];
-    return;
-  }
-  float4 x = iv.x[i];
-  float4 past = iv.past_x[i];
-  if (action & JA_ACCEPT) {
-    past = x;
-    iv.past_x[i] = x;
-  }
-  if (action & JA_UPDATE) {
-    const float omega = 0.75f;
-    const float4 r = iv.r[i], dg = iv.diag[i];
-    // b_k - sum_j A_ij x_j + a_ii x_i[k]  ==  r_k + a_ii x_k
-    x.x = fabsf(dg.x) < 1e-6f ? 0.f : omega * (r.x + dg.x * x.x) / dg.x + (1.f - omega) * past.x;
-    x.y = fabsf(dg.y) < 1e-6f ? 0.f : omega * (r.y + dg.y * x.y) / dg.y + (1.f - omega) * past.y;
-    x.z = fabsf(dg.z) < 1e-6f ? 0.f : omega * (r.z + dg.z * x.z) / dg.z + (1.f - omega) * past.z;
-    iv.x[i] = x;
-  }
+  if (i >= n) return;
+  const int ans = sc->terminal ? sc->ans : sc->cur;   // not terminal: the iteration budget of the caller ran out
+  const float4* src = ans == 3 ? iv.past_x : (ans == 0 ? iv.x : (ans == 1 ? iv.tmp : iv.r));
+  const float4 v = src[i];
+  iv.x[i] = v;
+  if (!sc->keep_past) iv.past_x[i] = v;
 }
 
 __global__ void __launch_bounds__(256) k_copy_xyz(int n, const float4* src, float4* dst) {
@@ -315,8 +365,21 @@ void launch_scalars_reset(const LaunchCfg& c, SolveScalars* sc) {
 }
 void launch_cg_init(const LaunchCfg& c, int n_vert, ImplicitVecs iv, const float4* rhs, const float4* opx,
                     double* red, RedMask mask) {
-  k_cg_init<<<nblk(n_vert), 256, 0, c.stream>>>(n_vert, iv, rhs, opx, red, mask);
+  launch_cg_init_ex(c, n_vert, iv, rhs, opx, red, mask, 0);
+}
+void launch_cg_init_ex(const LaunchCfg& c, int n_vert, ImplicitVecs iv, const float4* rhs, const float4* opx,
+                       double* red, RedMask mask, int zero_ps) {
+  k_cg_init<<<nblk(n_vert), 256, 0, c.stream>>>(n_vert, iv, rhs, opx, red, mask, zero_ps);
   note_launch("cg_init", c.stream);
+}
+void launch_cgcg_scalar(const LaunchCfg& c, int n_g, const double* red_g, int n_d, const double* red_d, SolveScalars* sc,
+                        float tol, int max_iter, const PeerComm& pc) {
+  k_cgcg_scalar<<<1, kFinalThreads, 0, c.stream>>>(n_g, red_g, n_d, red_d, sc, tol, max_iter, pc);
+  note_launch("cgcg_scalar", c.stream);
+}
+void launch_cgcg_finish(const LaunchCfg& c, int n_vert, ImplicitVecs iv, const SolveScalars* sc) {
+  k_cgcg_finish<<<nblk(n_vert), 256, 0, c.stream>>>(n_vert, iv, sc);
+  note_launch("cgcg_finish", c.stream);
 }
 void launch_cg_delta0(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc, float tol, int max_iter,
                       const PeerComm& pc) {
@@ -345,9 +408,9 @@ void launch_jacobi_decide(const LaunchCfg& c, int n_red, const double* red, Solv
   k_jacobi_decide<<<1, kFinalThreads, 0, c.stream>>>(n_red, red, sc, tol, max_iter, fixed, pc);
   note_launch("jacobi_decide", c.stream);
 }
-void launch_jacobi_update(const LaunchCfg& c, int n_vert, ImplicitVecs iv, SolveScalars* sc) {
-  k_jacobi_update<<<nblk(n_vert), 256, 0, c.stream>>>(n_vert, iv, sc);
-  note_launch("jacobi_update", c.stream);
+void launch_jacobi_finish(const LaunchCfg& c, int n_vert, ImplicitVecs iv, const SolveScalars* sc) {
+  k_jacobi_finish<<<nblk(n_vert), 256, 0, c.stream>>>(n_vert, iv, sc);
+  note_launch("jacobi_finish", c.stream);
 }
 void launch_copy_xyz(const LaunchCfg& c, int n, const float4* src, float4* dst) {
   k_copy_xyz<<<nblk(n), 256, 0, c.stream>>>(n, src, dst);

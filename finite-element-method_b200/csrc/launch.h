@@ -30,12 +30,20 @@ struct KinArgs {           // kinematic.py:14-45 / implicit.py:407-437 constants
 
 struct ImplicitVecs {      // object.py:83-93 vectors, float4 per vertex
   float4 *b, *x, *past_x, *d, *r, *q, *atb, *tmp, *diag;
+  float4 *w;               // single-reduction CG: w = Op r (d doubles as p, q as s = Op p)
 };
 
 struct SolveScalars {      // device-resident solver state (one per object)
   double delta_new, delta_old, dq, err, p_err;
   float alpha, beta;
   int iters, done, terminal, action, first;
+  // fused Jacobi (kernels_implicit.cu: OpJacobi): the iterate rotates through three buffers
+  int cur;                 // buffer holding the iterate the current pass evaluates
+  int ans;                 // terminal: buffer holding the answer (3 = past_x itself: revert before any accept)
+  int keep_past;           // terminal: past_vec_x keeps its (stale) value
+  // single-reduction CG (api_solve.cu): the vector update of iteration i is applied by the first pass of i+1
+  double gamma_old;        // r.r of the previous iteration
+  int pending;             // an update (alpha, beta) has been scheduled and not yet applied to x, r, p, s
 };
 
 enum ExplicitMode { EX_GRAD = 0, EX_STEP = 1, EX_ENERGY = 2 };
@@ -144,9 +152,23 @@ void launch_cg_update_xr(const LaunchCfg& c, int n_vert, ImplicitVecs iv, double
 void launch_cg_beta(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc, float tol, int max_iter,
                     const PeerComm& pc);
 void launch_cg_update_d(const LaunchCfg& c, int n_vert, ImplicitVecs iv, const SolveScalars* sc);
+// single-reduction (Chronopoulos-Gear) CG on A^T A
+//   first pass of an iteration: applies the pending update (p, s, x, r) in its vertex prologue, tmp = A r, partials of r.r
+void launch_cgcg_first(int dim, const LaunchCfg& c, const DevTiling& tl, Planes h, VertexState vs, float dt,
+                       ImplicitVecs iv, double* red, const SolveScalars* sc);
+//   gamma = sum red_g, delta = sum red_d -> alpha, beta, loop test; kind 0: x = b start (zero p, s handled by cg_init)
+void launch_cgcg_scalar(const LaunchCfg& c, int n_g, const double* red_g, int n_d, const double* red_d, SolveScalars* sc,
+                        float tol, int max_iter, const PeerComm& pc);
+void launch_cgcg_finish(const LaunchCfg& c, int n_vert, ImplicitVecs iv, const SolveScalars* sc);
+void launch_cg_init_ex(const LaunchCfg& c, int n_vert, ImplicitVecs iv, const float4* rhs, const float4* opx,
+                       double* red, RedMask mask, int zero_ps);
 void launch_jacobi_decide(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc, float tol,
                           int max_iter, int fixed, const PeerComm& pc);
-void launch_jacobi_update(const LaunchCfg& c, int n_vert, ImplicitVecs iv, SolveScalars* sc);
+void launch_jacobi_finish(const LaunchCfg& c, int n_vert, ImplicitVecs iv, const SolveScalars* sc);
+// one fused Jacobi pass: r = b - A x_k (norm^2 -> red) and, speculatively, x_{k+1} into the next of the three
+// rotating buffers {iv.x, iv.tmp, iv.r} (sc->cur says which holds x_k)
+void launch_jacobi_pass(int dim, const LaunchCfg& c, const DevTiling& tl, Planes h, VertexState vs, float dt,
+                        ImplicitVecs iv, double* red, const SolveScalars* sc);
 void launch_scalars_reset(const LaunchCfg& c, SolveScalars* sc);
 
 // misc vector ops

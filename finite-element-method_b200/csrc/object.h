@@ -59,7 +59,7 @@ struct SolveProgram {
   size_t pc = 0;
   bool in_prologue = true;
   int iters_issued = 0;
-  int method = 0, max_iter = 0;
+  int method = 0, max_iter = 0, pre = 0;
   bool fixed = false;
 };
 
@@ -78,6 +78,7 @@ struct femb_object {
   femb::ImplicitVecs iv{};
   float* d_phi = nullptr;           // per slot
   double* d_red = nullptr;
+  double* d_red2 = nullptr;         // second partial buffer (single-reduction CG: r.r of the first pass)
   int red_slots = 0;
   double* d_U = nullptr;
   femb::SolveScalars* d_sc = nullptr;

@@ -23,6 +23,7 @@
 
 #include <stdexcept>
 #include <string>
+#include <type_traits>
 
 namespace femb {
 
@@ -72,6 +73,26 @@ __device__ __forceinline__ float block_sum(float v, float* s_warp) {
     r = warp_sum(r);
   }
   return r;
+}
+
+// Ops with a vertex PROLOGUE (Op::PROLOGUE = true) transform a vertex's state when it is loaded: the thread that
+// OWNS the vertex (interior: the staging thread of its only tile; boundary: k_boundary) applies the transformation
+// in place and may add to the pass's reduction, every other reader only evaluates it.
+//   Op::load_vertex_ex(args, gid, own, red)
+template <class Op, class = void>
+struct has_prologue : std::false_type {};
+template <class Op>
+struct has_prologue<Op, std::void_t<decltype(Op::PROLOGUE)>> : std::bool_constant<Op::PROLOGUE> {};
+
+template <class Op>
+__device__ __forceinline__ float4 stage_vertex(const typename Op::Args& a, const LocalVert& v, float& red) {
+  if constexpr (has_prologue<Op>::value) return Op::load_vertex_ex(a, v.gid, v.part < 0, red);
+  else return Op::load_vertex(a, v.gid);
+}
+template <class Op>
+__device__ __forceinline__ float4 own_vertex(const typename Op::Args& a, int gid, float& red) {
+  if constexpr (has_prologue<Op>::value) return Op::load_vertex_ex(a, gid, true, red);
+  else return Op::load_vertex(a, gid);
 }
 
 // the three float4 of one element slot, loaded with streaming (no L1 allocate) loads
@@ -252,17 +273,17 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile_persistent(Dev
   // vertex values of the tile about to be processed: two per thread in registers, the rest (tiles with
   // more than 2*B local vertices: irregular meshes only) fetched directly at staging time
   float4 vreg0 = make_float4(0.f, 0.f, 0.f, 0.f), vreg1 = vreg0;
+  float red = 0.f;
   if constexpr (AV) {
     const int n_lv = s_td[0].n_lv;
     for (int l = tid; l < n_lv; l += B) cp_async16(&sv0[l], Op::vertex_src(a) + lv_buf(0)[l].gid);
     cp_async_commit();
   } else {
     const int n_lv = s_td[0].n_lv;
-    if (tid < n_lv) vreg0 = Op::load_vertex(a, lv_buf(0)[tid].gid);
-    if (tid + B < n_lv) vreg1 = Op::load_vertex(a, lv_buf(0)[tid + B].gid);
+    if (tid < n_lv) vreg0 = stage_vertex<Op>(a, lv_buf(0)[tid], red);
+    if (tid + B < n_lv) vreg1 = stage_vertex<Op>(a, lv_buf(0)[tid + B], red);
   }
 
-  float red = 0.f;
   for (int k = 0;; ++k) {
     const int b = k & 1;
     const DevTile& td = s_td[b];          // read on demand from shared memory (keeps registers for the math)
@@ -297,7 +318,7 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile_persistent(Dev
     } else {
       if (tid < td.n_lv) sv[tid] = vreg0;
       if (tid + B < td.n_lv) sv[tid + B] = vreg1;
-      for (int l = tid + 2 * B; l < td.n_lv; l += B) sv[l] = Op::load_vertex(a, s_lv[l].gid);
+      for (int l = tid + 2 * B; l < td.n_lv; l += B) sv[l] = stage_vertex<Op>(a, s_lv[l], red);
     }
     __syncthreads();
 
@@ -328,8 +349,8 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile_persistent(Dev
         for (int l = tid; l < n_lv; l += B) cp_async16(&svn[l], Op::vertex_src(a) + nlv[l].gid);
         cp_async_commit();
       } else {
-        if (tid < n_lv) vreg0 = Op::load_vertex(a, nlv[tid].gid);
-        if (tid + B < n_lv) vreg1 = Op::load_vertex(a, nlv[tid + B].gid);
+        if (tid < n_lv) vreg0 = stage_vertex<Op>(a, nlv[tid], red);
+        if (tid + B < n_lv) vreg1 = stage_vertex<Op>(a, nlv[tid + B], red);
       }
     }
     mbar_wait(&s_bar[2], (uint32_t)(k & 1));
@@ -421,10 +442,10 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile(DevTiling tl, 
   __syncthreads();          // barrier words initialised before anyone polls them
   mbar_wait(&s_bar[0], 0);
 
-  for (int l = threadIdx.x; l < td.n_lv; l += B) sv[l] = Op::load_vertex(a, s_lv[l].gid);
+  float red = 0.f;
+  for (int l = threadIdx.x; l < td.n_lv; l += B) sv[l] = stage_vertex<Op>(a, s_lv[l], red);
   __syncthreads();
 
-  float red = 0.f;
   auto one = [&](int e, const typename Op::Elem& d) {
     float out[Op::NSTAGE];
     Op::compute(a, td.slot_off + e, d, sv, out, red);
@@ -494,7 +515,7 @@ __global__ void __launch_bounds__(kBoundaryBlock) k_boundary(DevTiling tl, typen
     const int s0 = tl.bptr[b], s1 = tl.bptr[b + 1] - (hk >= 0 ? 1 : 0);
     const int gid = tl.n_interior + b;
     // the vertex operands do not depend on the partial sums: request them first
-    const float4 vtx = Op::load_vertex(a, gid);
+    const float4 vtx = own_vertex<Op>(a, gid, red);
     const float4 pre = Op::pre(a, gid);
     // Launched with programmatic stream serialization: everything above overlaps the tail of the tile
     // kernel; the partial sums it wrote are visible only after this wait (no-op in a plain launch).

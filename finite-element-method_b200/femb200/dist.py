@@ -186,7 +186,7 @@ class SlabHalo:
         self.send = torch.zeros((self.n, 4), dtype=torch.float32, device=device or "cuda")
         self.recv = torch.zeros((self.n, 4), dtype=torch.float32, device=device or "cuda")
         handle.halo_bind(self.send.data_ptr(), self.recv.data_ptr())
-        self.allred = torch.zeros(1, dtype=torch.float64, device=device or "cuda")
+        self.allred = torch.zeros(4, dtype=torch.float64, device=device or "cuda")   # up to 4 sums per all-reduce
         handle.reduce_bind(self.allred.data_ptr())
         handle.halo_mass(1)
         self.exchange()
@@ -274,7 +274,8 @@ class SlabHalo:
             return handle.implicit_solve(dt, method, preconditioned, max_iter, tol, fetch=fetch)
         fixed = (tol == 0.0)
         n_cap = max_iter if max_iter > 0 else (500 if method == 1 else 20000)
-        n_it = n_cap if method == 1 else n_cap + 2
+        # single-reduction CG (A^T A) sees r.r of update k in iteration k + 1; Jacobi needs 2 more passes (api_solve.cu)
+        n_it = (n_cap + (1 if (preconditioned == 1 and not fixed) else 0)) if method == 1 else n_cap + 2
         handle.solve_begin(dt, method, preconditioned, max_iter, tol)
         self._until_iter(handle)                       # prologue: assemble, A^T b, initial residual
         graph = None

@@ -107,7 +107,7 @@ def test_cuda_path_matches_reference_fixture(name):
         # the solve: both sides stop at an ABSOLUTE residual (r.r <= 1e-5 / ||b - Ax|| <= 1e-5), so x agrees to that level
         report["x"] = rel(out["x"][0], fx["s_x"][0])
         assert report["x"] <= 5e-3
-        assert all(1 <= it <= 20000 for it in iters)
+        assert all(0 <= it <= 20000 for it in iters)
     # trajectories: every recorded step up to the end (100 steps where the case has them)
     for k, step in enumerate(rec):
         tol = POS_TOL

@@ -71,3 +71,27 @@ def test_weld_merges_duplicates_keeps_order():
     wv, wf = meshio.weld(v, f)
     assert wv.tolist() == [[0, 0, 0], [1, 0, 0], [0, 1, 0]]
     assert wf.tolist() == [[0, 1, 2], [0, 1, 2]]          # the degenerate third triangle is dropped
+
+
+@pytest.mark.parametrize("name", ["k4_analytic", "spot_analytic", "spot100_cg"])
+def test_boundary_faces_equal_the_reference_extract_surface(name):
+    """meshgen.boundary_faces against the surface the REFERENCE's own Object.extract_surface (object.py:255-308)
+    produced for the same tets (stored in the reference fixtures, tests/golden/make_ref_golden.py): same triangles,
+    same winding."""
+    import ref_fixtures as rf
+    fx = rf.load(name)
+    bf = meshgen.boundary_faces(fx["raw_verts"].astype(np.float64), fx["elems"])
+
+    def canon(F):
+        return set(tuple(np.roll(f, -int(np.argmin(f)))) for f in np.asarray(F).tolist())
+    assert canon(bf) == canon(fx["faces"]) and len(bf) == len(fx["faces"])
+
+
+@pytest.mark.parametrize("name,nv,nf", [("spot100.obj", 119, 234), ("spot.obj", 587, 1170), ("cube.stl", 8, 12)])
+def test_tetrahedralize_reference_assets(name, nv, nf):
+    """The assets BASELINE configs 2 and 5 name (reference obj/, vendored as input data) and the binary STL."""
+    nodes, tets, (sv, sf) = meshio.tetrahedralize_file(os.path.join(OBJ, name))
+    assert len(sv) == nv and len(sf) == nf
+    assert np.array_equal(nodes[:len(sv)], sv.astype(np.float32))
+    vol = np.abs(_tet_volumes(nodes, tets))
+    assert (vol > 0).all() and abs(vol.sum() - _surface_volume(sv, sf)) / _surface_volume(sv, sf) < 0.03
