@@ -515,6 +515,7 @@ int femb_peer_bind(femb_object* o, const femb_peer_desc* d) {
     o->d_halo_dev = fused ? d_hd : nullptr;
     o->n_send_ctas = std::max(1, std::min(o->cfg.sms, (o->halo.n + 1023) / 1024));
     if (const char* w = std::getenv("FEMB_PEER_FUSED_WAVES")) o->fuse_max_waves = std::atoi(w);
+    if (const char* m = std::getenv("FEMB_PEER_MODE")) o->late_send = fused && std::string(m) == "late";
   }
   FEMB_CUDA(cudaStreamSynchronize(o->stream));
   o->peer = pc;

@@ -8,6 +8,7 @@
 // femb_implicit_solve_begin / _advance / _finish hand the communication points to a
 // caller that owns the collectives (one process per GPU, torch.distributed / NCCL).
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 #include "object.h"
@@ -30,7 +31,7 @@ constexpr bool kApplyPersist = FEMB_PERSIST_APPLY != 0;   // the operator passes
 
 static int apply_red_slots(const femb_object* o) {
   const bool fused = o->fused_pass(kApplyPersist);   // fused exchange: one CTA per tile (object.h: peer_pass)
-  return apply_tile_grid(o->dtl, o->pass_split(), !fused) + (o->dtl.n_boundary + 255) / 256;
+  return apply_tile_grid(o->dtl, o->split_reds(), !fused) + (o->dtl.n_boundary + 255) / 256;
 }
 
 static void poll(femb_object* o) {
@@ -137,7 +138,7 @@ void build_program(femb_object* o, SolveProgram& P, float dt, int method, int pr
   if (tol < 0.f) tol = 1e-5f;                          // implicit.py:236,341
   if (max_iter <= 0) max_iter = method == 1 ? 500 : 20000;  // implicit.py:337,237
   P.method = method;
-  P.pre = preconditioned == 1 ? 1 : 0;
+  P.pre = 0;   // set below: 1 when the single-reduction CG arrangement is chosen
   o->last_method = method;
   P.max_iter = max_iter;
   const float ktol = P.fixed ? -1.f : tol;
@@ -171,20 +172,44 @@ void build_program(femb_object* o, SolveProgram& P, float dt, int method, int pr
     } else {
       pro.pass(apply(0, iv.b, iv.q, AP_PLAIN, nullptr, nullptr, nullptr), kApplyPersist);
     }
-    const int cgcg = preconditioned == 1 ? 1 : 0;   // A^T A: single-reduction CG (OpCgFirst); plain A: the textbook loop
+    // A^T A variant: textbook loop or the single-reduction arrangement (below).  Measured on C4, one GPU: 0.583 vs
+    // 0.624 ms per iteration -- the merged vector kernel streams nine 43 MB vectors from HBM where the textbook
+    // kernels find most of theirs in L2 -- so the single-reduction form is used only where a rank's vectors are
+    // L2-resident and the launch / all-sum count is what costs (thin slabs).  FEMB_CG_SINGLE_REDUCTION=0|1 overrides.
+    int cgcg = 0;
+    if (preconditioned == 1) {
+      cgcg = dist && (size_t)nv * sizeof(float4) * 9 <= (size_t)64 << 20;
+      if (const char* e = std::getenv("FEMB_CG_SINGLE_REDUCTION")) cgcg = e[0] == '1';
+    }
     pro.add([=] { launch_cg_init_ex(o->cfg, nv, iv, rhs, iv.q, o->d_red, mask, cgcg); });   // x = b, r = rhs - op(x), d = r
     pro.gsum(vred, [=](int n, const double* red, const PeerComm& pc) { launch_cg_delta0(o->cfg, n, red, sc, ktol, max_iter, pc); });
+    if (cgcg)   // the first iteration's gamma: the same partials, where the iteration's scalar kernel looks for them
+      pro.add([=] { FEMB_CUDA(cudaMemcpyAsync(o->d_red2, o->d_red, (size_t)vred * sizeof(double), cudaMemcpyDeviceToDevice, o->stream)); });
 
-    if (cgcg) {
-      // iteration = [pending update + tmp = A r, partials of r.r] [w = A^T tmp, partials of r.w] [scalars]
-      it.pass([o, dim, dt, sc](const LaunchCfg& c) {
-        launch_cgcg_first(dim, c, o->dtl, o->h, o->vs, dt, o->iv, o->d_red2, sc);
-      }, kApplyPersist);
+    if (preconditioned == 1 && !cgcg) {
+      it.pass(apply(0, iv.d, iv.tmp, AP_PLAIN, nullptr, nullptr, sc), kApplyPersist);
+      it.pass(apply(1, iv.tmp, iv.q, AP_DOT, iv.d, nullptr, sc), kApplyPersist);
+      it.gsum(ared, [=](int n, const double* red, const PeerComm& pc) { launch_cg_alpha(o->cfg, n, red, sc, pc); });
+      it.add([=] { launch_cg_update_xr(o->cfg, nv, iv, o->d_red, sc, mask); });
+      it.gsum(vred, [=](int n, const double* red, const PeerComm& pc) { launch_cg_beta(o->cfg, n, red, sc, ktol, max_iter, pc); });
+      it.add([=] { launch_cg_update_d(o->cfg, nv, iv, sc); });
+    } else if (cgcg) {
+      P.pre = 1;
+      // Single-reduction CG (Chronopoulos & Gear) -- algebraically the loop of implicit.py:341-386:
+      //   w = Op r ; gamma = r.r ; delta = r.w ; beta = gamma / gamma_old ; alpha = gamma / (delta - beta gamma / alpha_old)
+      //   p = r + beta p ; s = w + beta s ; x += alpha p ; r -= alpha s                 (s = Op p by linearity)
+      // Both dot products are consumed at ONE point, so an iteration is: two operator passes, one scalar kernel
+      // (one all-sum on a slab instead of two), one streaming vector kernel -- 6 launches instead of 8.
+      // gamma's partials come from the vector kernel of the previous iteration (cg_init for the first).
+      // (Folding the vector updates into the first pass's vertex loads was measured: 0.649 vs 0.583 ms per
+      // iteration on C4 -- the tile kernels are latency-bound, the streaming kernel runs at the HBM roof.)
+      it.pass(apply(0, iv.r, iv.tmp, AP_PLAIN, nullptr, nullptr, sc), kApplyPersist);
       it.pass(apply(1, iv.tmp, iv.w, AP_DOT, iv.r, nullptr, sc), kApplyPersist);
-      it.gsum2(ared, o->d_red2, ared, o->d_red,
+      it.gsum2(vred, o->d_red2, ared, o->d_red,
                [=](int na, const double* ra, int nb, const double* rb, const PeerComm& pc) {
                  launch_cgcg_scalar(o->cfg, na, ra, nb, rb, sc, ktol, max_iter, pc);
                });
+      it.add([=] { launch_cgcg_update(o->cfg, nv, iv, o->d_red2, sc, mask); });
     } else {
       it.pass(apply(0, iv.d, iv.q, AP_DOT, iv.d, nullptr, sc), kApplyPersist);
       it.gsum(ared, [=](int n, const double* red, const PeerComm& pc) { launch_cg_alpha(o->cfg, n, red, sc, pc); });
@@ -227,7 +252,6 @@ void check_solve_args(femb_object* o, int method) {
 
 void finish(femb_object* o, int32_t* iters_out, float* resid_out) {
   if (o->prog->method == 0) launch_jacobi_finish(o->cfg, o->n_vert, o->iv, o->d_sc);   // answer buffer -> vec_x, past_vec_x
-  if (o->prog->method == 1 && o->prog->pre) launch_cgcg_finish(o->cfg, o->n_vert, o->iv, o->d_sc);   // a scheduled, unapplied update
   launch_copy_xyz(o->cfg, o->n_vert, o->iv.x, o->vs.vel);          // vel = x (222-223)
   if (iters_out || resid_out) {
     poll(o);

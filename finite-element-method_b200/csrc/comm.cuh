@@ -83,12 +83,13 @@ __device__ __forceinline__ uint32_t halo_recv_begin(const PeerComm& pc, uint32_t
   }
   return seq & 1u;
 }
-__device__ __forceinline__ void halo_recv_end(const PeerComm& pc, uint32_t seq) {
+// n_ctas: CTAs of the grid that call this (the boundary kernel's sender CTAs do not)
+__device__ __forceinline__ void halo_recv_end(const PeerComm& pc, uint32_t seq, unsigned n_ctas) {
   CommState* st = pc.st;
   __syncthreads();
   if (threadIdx.x == 0) {
     const unsigned prev = atomicAdd(&st->unpack_count, 1u);
-    if (prev == gridDim.x - 1) {
+    if (prev == n_ctas - 1) {
       st->unpack_count = 0;
       st->recv_seq = seq;
     }

@@ -254,7 +254,8 @@ struct OpJacobi {
   struct Args {
     Planes h;
     const float4* pos;     // .w = mass
-    float4* xb[3];
+    float4 *x0, *x1, *x2;  // the three rotating iterate buffers (selected with compares: a dynamically indexed
+                           // pointer array in the kernel arguments would put the whole struct in local memory)
     const float4* b;
     const float4* diag;
     const float4* past;
@@ -268,7 +269,9 @@ struct OpJacobi {
   __device__ static float w0() { return 0.f; }
   __device__ static float4* partial_buf(const Args& a) { return a.partial; }
   __device__ static double* red_buf(const Args& a) { return a.red; }
-  __device__ static const float4* in_buf(const Args& a) { return a.xb[a.sc->cur]; }
+  __device__ static int cur_of(const Args& a) { return __ldg(&a.sc->cur); }
+  __device__ static float4* buf(const Args& a, int i) { return i == 0 ? a.x0 : (i == 1 ? a.x1 : a.x2); }
+  __device__ static const float4* in_buf(const Args& a) { return buf(a, cur_of(a)); }
   __device__ static float4 load_vertex(const Args& a, int gid) { return in_buf(a)[gid]; }
   using Elem = PlaneElem;
   __device__ static void prefetch(const Args& a, int slot, uint32_t bytes) { prefetch_planes(a.h, slot, bytes, D == 3); }
@@ -298,8 +301,8 @@ struct OpJacobi {
   __device__ static void vertex(const Args& a, int gid, float4 x, float4 b, const float (&acc)[D], float& red) {
     const float s = a.dt2 * (1.f / a.pos[gid].w);
     const float4 dg = a.diag[gid];
-    const int cur = a.sc->cur;
-    const float4 past = a.sc->first ? a.past[gid] : x;
+    const int cur = cur_of(a);
+    const float4 past = __ldg(&a.sc->first) ? a.past[gid] : x;
     float r[3] = {0.f, 0.f, 0.f};
     const float xv[3] = {x.x, x.y, x.z}, bv[3] = {b.x, b.y, b.z}, dv[3] = {dg.x, dg.y, dg.z}, pv[3] = {past.x, past.y, past.z};
     float xn[3] = {0.f, 0.f, 0.f};
@@ -310,120 +313,17 @@ struct OpJacobi {
       red += r[i] * r[i];
       xn[i] = fabsf(dv[i]) < 1e-6f ? 0.f : omega * (r[i] + dv[i] * xv[i]) / dv[i] + (1.f - omega) * pv[i];
     }
-    a.xb[cur == 2 ? 0 : cur + 1][gid] = make_float4(xn[0], xn[1], xn[2], 0.f);
+    buf(a, cur == 2 ? 0 : cur + 1)[gid] = make_float4(xn[0], xn[1], xn[2], 0.f);
   }
 };
-
-// ---------------------------------------------------------------------------
-// Single-reduction CG (Chronopoulos & Gear) on A^T A x = A^T b -- algebraically the CG loop of implicit.py:341-386:
-//   w = Op r ; gamma = r.r ; delta = r.w ; beta = gamma / gamma_old ; alpha = gamma / (delta - beta gamma / alpha_old)
-//   p = r + beta p ; s = w + beta s ; x += alpha p ; r -= alpha s                    (s = Op p by linearity)
-// Both dot products are known at ONE point of the iteration, and the four vector updates need nothing else -- so they
-// are not a kernel: the FIRST operator pass of the next iteration applies them in its vertex prologue, on the fly,
-// while it loads r as the operator's input (owner threads write p, s, x, r back; other tiles that read a shared
-// vertex only evaluate r).  An iteration is: this pass (tmp = A r, partials of r.r), the A^T pass with the r.w
-// epilogue (OpApply<TR=1>, AP_DOT), one scalar kernel.  3 kernels + 2 boundary kernels instead of 8, one
-// synchronisation point (one all-sum on a slab) instead of two.
-// ---------------------------------------------------------------------------
-template <int D>
-struct OpCgFirst {
-  static constexpr bool PERSIST = FEMB_PERSIST_APPLY != 0;
-  static constexpr bool ASYNC_VERTEX = false;
-  static constexpr bool PROLOGUE = true;
-  static constexpr int BLOCK = kBlock, MIN_CTAS = kMinCtas, NSTAGE = D * D, GATHER = G_STAR;
-  static constexpr bool REDUCE = true;
-  struct Args {
-    Planes h;
-    const float4* pos;     // .w = mass
-    ImplicitVecs iv;       // x, r, d (= p), q (= s), w updated in place; tmp = A r written
-    float4* partial;
-    float dt2;
-    double* red;
-    const SolveScalars* sc;
-  };
-  __device__ static bool early_exit(const Args& a) { return (a.sc->done | a.sc->terminal) != 0; }
-  __host__ __device__ static bool itc(const Args&) { return false; }
-  __device__ static float w0() { return 0.f; }
-  __device__ static float4* partial_buf(const Args& a) { return a.partial; }
-  __device__ static double* red_buf(const Args& a) { return a.red; }
-  __device__ static float4 load_vertex(const Args& a, int gid) {
-    float dummy = 0.f;
-    return load_vertex_ex(a, gid, false, dummy);
-  }
-  // r after the pending update; the owner also writes p, s, x, r and counts r.r
-  __device__ static float4 load_vertex_ex(const Args& a, int gid, bool own, float& red) {
-    float4 r = a.iv.r[gid];
-    if (a.sc->pending) {
-      const float alpha = a.sc->alpha, beta = a.sc->beta;
-      const float4 w = a.iv.w[gid], s0 = a.iv.q[gid];
-      const float4 s = make_float4(w.x + beta * s0.x, w.y + beta * s0.y, w.z + beta * s0.z, 0.f);
-      const float4 rn = make_float4(r.x - alpha * s.x, r.y - alpha * s.y, r.z - alpha * s.z, 0.f);
-      if (own) {
-        const float4 p0 = a.iv.d[gid];
-        float4 x = a.iv.x[gid];
-        const float4 p = make_float4(r.x + beta * p0.x, r.y + beta * p0.y, r.z + beta * p0.z, 0.f);
-        x.x += alpha * p.x; x.y += alpha * p.y; x.z += alpha * p.z;
-        a.iv.d[gid] = p;
-        a.iv.q[gid] = s;
-        a.iv.x[gid] = x;
-        a.iv.r[gid] = rn;
-      }
-      r = rn;
-    }
-    if (own) red += r.x * r.x + r.y * r.y + (D == 3 ? r.z * r.z : 0.f);
-    return r;
-  }
-  using Elem = PlaneElem;
-  __device__ static void prefetch(const Args& a, int slot, uint32_t bytes) { prefetch_planes(a.h, slot, bytes, D == 3); }
-  __device__ static void prefetch_verts(const Args& a, int base, uint32_t bytes) {
-    bulk_prefetch_l2(a.iv.r + base, bytes);
-    bulk_prefetch_l2(a.iv.w + base, bytes);
-    bulk_prefetch_l2(a.iv.q + base, bytes);
-    bulk_prefetch_l2(a.iv.d + base, bytes);
-    bulk_prefetch_l2(a.iv.x + base, bytes);
-  }
-  __device__ static void load(const Args& a, int slot, Elem& d) { load_planes<D>(a.h, slot, d); }
-  __device__ static void compute(const Args&, int, const Elem& d, const float4* sv, float (&out)[NSTAGE], float&) {
-    const float4 h0 = d.a, h1 = d.b, h2 = d.c;
-    Mat<D> H, E;
-    unpack_h<D>(h0, h1, h2, H);
-    edge_matrix<D>(sv, __float_as_uint(h0.x), __float_as_uint(h0.y), E);
-#pragma unroll
-    for (int j = 0; j < D; ++j)
-#pragma unroll
-      for (int i = 0; i < D; ++i) {
-        float s = H.m[i][0] * E.m[0][j];
-#pragma unroll
-        for (int k = 1; k < D; ++k) s += H.m[i][k] * E.m[k][j];
-        out[j * D + i] = s;
-      }
-  }
-  __device__ static float4 pre(const Args& a, int gid) { return a.pos[gid]; }
-  // tmp = A r = r - dt^2 M^-1 K r       (vtx = the operator's input r, pos.w = mass)
-  __device__ static void vertex(const Args& a, int gid, float4 r, float4 pos, const float (&acc)[D], float&) {
-    const float s = a.dt2 * (1.f / pos.w);
-    a.iv.tmp[gid] = make_float4(r.x - s * acc[0], r.y - s * acc[1], D == 3 ? r.z - s * acc[D - 1] : 0.f, 0.f);
-  }
-};
-
-void launch_cgcg_first(int dim, const LaunchCfg& c, const DevTiling& tl, Planes h, VertexState vs, float dt,
-                       ImplicitVecs iv, double* red, const SolveScalars* sc) {
-  if (dim == 3) {
-    OpCgFirst<3>::Args a{h, vs.pos, iv, vs.partial, dt * dt, red, sc};
-    run_tile_pass<3, OpCgFirst<3>>("cgcg_first", c, tl, a);
-  } else {
-    OpCgFirst<2>::Args a{h, vs.pos, iv, vs.partial, dt * dt, red, sc};
-    run_tile_pass<2, OpCgFirst<2>>("cgcg_first", c, tl, a);
-  }
-}
 
 void launch_jacobi_pass(int dim, const LaunchCfg& c, const DevTiling& tl, Planes h, VertexState vs, float dt,
                         ImplicitVecs iv, double* red, const SolveScalars* sc) {
   if (dim == 3) {
-    OpJacobi<3>::Args a{h, vs.pos, {iv.x, iv.tmp, iv.r}, iv.b, iv.diag, iv.past_x, vs.partial, dt * dt, red, sc};
+    OpJacobi<3>::Args a{h, vs.pos, iv.x, iv.tmp, iv.r, iv.b, iv.diag, iv.past_x, vs.partial, dt * dt, red, sc};
     run_tile_pass<3, OpJacobi<3>>("jacobi_pass", c, tl, a);
   } else {
-    OpJacobi<2>::Args a{h, vs.pos, {iv.x, iv.tmp, iv.r}, iv.b, iv.diag, iv.past_x, vs.partial, dt * dt, red, sc};
+    OpJacobi<2>::Args a{h, vs.pos, iv.x, iv.tmp, iv.r, iv.b, iv.diag, iv.past_x, vs.partial, dt * dt, red, sc};
     run_tile_pass<2, OpJacobi<2>>("jacobi_pass", c, tl, a);
   }
 }

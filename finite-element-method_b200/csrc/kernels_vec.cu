@@ -133,7 +133,6 @@ __global__ void __launch_bounds__(kFinalThreads) k_cgcg_scalar(int n_g, const do
   const bool go = sc->iters < max_iter && (tol < 0.f || (float)g > tol);
   if (!go) {
     sc->done = 1;
-    sc->pending = 0;
     return;
   }
   float alpha, beta;
@@ -151,19 +150,30 @@ __global__ void __launch_bounds__(kFinalThreads) k_cgcg_scalar(int n_g, const do
   sc->pending = 1;
 }
 
-// end of a single-reduction CG solve: an update that was scheduled but never applied (fixed iteration count, or the
-// caller's iteration budget ran out) is applied to x here
-__global__ void __launch_bounds__(256) k_cgcg_finish(int n, ImplicitVecs iv, const SolveScalars* sc) {
-  if (!sc->pending) return;
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
+// The four vector updates of a single-reduction CG iteration in ONE streaming kernel, with the partials of the new
+// r.r:  p = r + beta p ; s = w + beta s ; x += alpha p ; r -= alpha s   (iv.d = p, iv.q = s = Op p)
+__global__ void __launch_bounds__(256) k_cgcg_update(int n, ImplicitVecs iv, double* red, const SolveScalars* sc,
+                                                     RedMask mask) {
+  __shared__ float s_warp[32];
+  if (sc->done) return;
   const float alpha = sc->alpha, beta = sc->beta;
-  const float4 r = iv.r[i], p0 = iv.d[i];
-  float4 x = iv.x[i];
-  x.x += alpha * (r.x + beta * p0.x);
-  x.y += alpha * (r.y + beta * p0.y);
-  x.z += alpha * (r.z + beta * p0.z);
-  iv.x[i] = x;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  float v = 0.f;
+  if (i < n) {
+    float4 r = iv.r[i], x = iv.x[i];
+    const float4 w = iv.w[i], s0 = iv.q[i], p0 = iv.d[i];
+    const float4 p = make_float4(r.x + beta * p0.x, r.y + beta * p0.y, r.z + beta * p0.z, 0.f);
+    const float4 s = make_float4(w.x + beta * s0.x, w.y + beta * s0.y, w.z + beta * s0.z, 0.f);
+    x.x += alpha * p.x; x.y += alpha * p.y; x.z += alpha * p.z;
+    r.x -= alpha * s.x; r.y -= alpha * s.y; r.z -= alpha * s.z;
+    iv.d[i] = p;
+    iv.q[i] = s;
+    iv.x[i] = x;
+    iv.r[i] = r;
+    v = counted(mask, i) ? dot3(r, r) : 0.f;
+  }
+  const float t = block_sum(v, s_warp);
+  if (threadIdx.x == 0) red[blockIdx.x] = (double)t;
 }
 
 // x += alpha d ; r -= alpha q ; partial r.r               (implicit.py:357-381)
@@ -377,9 +387,9 @@ void launch_cgcg_scalar(const LaunchCfg& c, int n_g, const double* red_g, int n_
   k_cgcg_scalar<<<1, kFinalThreads, 0, c.stream>>>(n_g, red_g, n_d, red_d, sc, tol, max_iter, pc);
   note_launch("cgcg_scalar", c.stream);
 }
-void launch_cgcg_finish(const LaunchCfg& c, int n_vert, ImplicitVecs iv, const SolveScalars* sc) {
-  k_cgcg_finish<<<nblk(n_vert), 256, 0, c.stream>>>(n_vert, iv, sc);
-  note_launch("cgcg_finish", c.stream);
+void launch_cgcg_update(const LaunchCfg& c, int n_vert, ImplicitVecs iv, double* red, const SolveScalars* sc, RedMask mask) {
+  k_cgcg_update<<<nblk(n_vert), 256, 0, c.stream>>>(n_vert, iv, red, sc, mask);
+  note_launch("cgcg_update", c.stream);
 }
 void launch_cg_delta0(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc, float tol, int max_iter,
                       const PeerComm& pc) {

@@ -43,7 +43,7 @@ struct SolveScalars {      // device-resident solver state (one per object)
   int keep_past;           // terminal: past_vec_x keeps its (stale) value
   // single-reduction CG (api_solve.cu): the vector update of iteration i is applied by the first pass of i+1
   double gamma_old;        // r.r of the previous iteration
-  int pending;             // an update (alpha, beta) has been scheduled and not yet applied to x, r, p, s
+  int pending;             // 1 after the first iteration of a single-reduction CG solve (beta is defined)
 };
 
 enum ExplicitMode { EX_GRAD = 0, EX_STEP = 1, EX_ENERGY = 2 };
@@ -63,6 +63,7 @@ struct LaunchCfg {
   int n_send = 0;                //   part 2: sender CTAs at the front of the tile kernel
   int fuse_recv = 0;             //   phase 2: the boundary kernel receives
   int no_persist = 0;            //   one CTA per tile even for Ops that default to the persistent kernel
+  int bnd_send = 0;              //   phase 2 with fuse_recv: sender CTAs at the front of the BOUNDARY kernel ("late send")
 };
 
 struct Halo {                    // vertices shared with a neighbouring rank (slab interface planes)
@@ -152,14 +153,12 @@ void launch_cg_update_xr(const LaunchCfg& c, int n_vert, ImplicitVecs iv, double
 void launch_cg_beta(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc, float tol, int max_iter,
                     const PeerComm& pc);
 void launch_cg_update_d(const LaunchCfg& c, int n_vert, ImplicitVecs iv, const SolveScalars* sc);
-// single-reduction (Chronopoulos-Gear) CG on A^T A
-//   first pass of an iteration: applies the pending update (p, s, x, r) in its vertex prologue, tmp = A r, partials of r.r
-void launch_cgcg_first(int dim, const LaunchCfg& c, const DevTiling& tl, Planes h, VertexState vs, float dt,
-                       ImplicitVecs iv, double* red, const SolveScalars* sc);
-//   gamma = sum red_g, delta = sum red_d -> alpha, beta, loop test; kind 0: x = b start (zero p, s handled by cg_init)
+// single-reduction (Chronopoulos-Gear) CG on A^T A (api_solve.cu)
+//   gamma = sum red_g, delta = sum red_d -> loop test, alpha, beta
 void launch_cgcg_scalar(const LaunchCfg& c, int n_g, const double* red_g, int n_d, const double* red_d, SolveScalars* sc,
                         float tol, int max_iter, const PeerComm& pc);
-void launch_cgcg_finish(const LaunchCfg& c, int n_vert, ImplicitVecs iv, const SolveScalars* sc);
+//   p = r + beta p ; s = w + beta s ; x += alpha p ; r -= alpha s ; partials of r.r -> red
+void launch_cgcg_update(const LaunchCfg& c, int n_vert, ImplicitVecs iv, double* red, const SolveScalars* sc, RedMask mask);
 void launch_cg_init_ex(const LaunchCfg& c, int n_vert, ImplicitVecs iv, const float4* rhs, const float4* opx,
                        double* red, RedMask mask, int zero_ps);
 void launch_jacobi_decide(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc, float tol,

@@ -151,10 +151,18 @@ struct femb_object {
   // fusion removes (N=2 on C4: 0.342 vs 0.370 ms per A^T A-CG iteration); on thin slabs it is the other way
   // round (the slab of N=8: 0.137 vs 0.123).  FEMB_PEER_FUSED_WAVES moves the threshold.
   int fuse_max_waves = 8;
+  // "late send" (FEMB_PEER_MODE=late): ONE tile kernel over all tiles (persistent where the Op wants it), then the
+  // boundary kernel whose first CTAs send the shared vertices' sums while the rest finish the ordinary boundary
+  // vertices; only CTAs that own a shared vertex wait for the neighbours.  Two kernels per pass, no split, no
+  // programmatic dependent launch; the NVLink latency hides behind the boundary kernel's own work.
+  bool late_send = false;
   bool fused_pass(bool persistent_op) const {
+    if (late_send) return false;
     if (!pass_split() || !d_halo_dev) return false;
     return !persistent_op || (dtl.n_tiles - dtl.n_halo_tiles) <= (long long)fuse_max_waves * dtl.grid;
   }
+  bool late_pass() const { return late_send && peer_on && d_halo_dev; }
+  bool split_reds() const { return pass_split() && !late_pass(); }   // tile partials laid out as two launches
   // One tile pass of a slab rank over peer memory.  f(cfg) launches the pass's kernels for the phase / part
   // in cfg.
   //   fused:   halo tiles | [sender CTAs + other tiles] (programmatic dependent launch) | boundary kernel that
@@ -167,6 +175,14 @@ struct femb_object {
     LaunchCfg c1 = cfg, c2 = cfg;
     c1.phase = 1;
     c2.phase = 2;
+    if (late_pass()) {
+      f(c1);                 // every tile, one launch
+      c2.hd = d_halo_dev;
+      c2.fuse_recv = 1;
+      c2.bnd_send = n_send_ctas;
+      f(c2);
+      return;
+    }
     if (fused_pass(persistent_op)) {
       c1.no_persist = c2.no_persist = 1;   // sender CTAs and persistent tile CTAs do not mix (run_tile_pass)
       c1.part = 1;

@@ -75,26 +75,6 @@ __device__ __forceinline__ float block_sum(float v, float* s_warp) {
   return r;
 }
 
-// Ops with a vertex PROLOGUE (Op::PROLOGUE = true) transform a vertex's state when it is loaded: the thread that
-// OWNS the vertex (interior: the staging thread of its only tile; boundary: k_boundary) applies the transformation
-// in place and may add to the pass's reduction, every other reader only evaluates it.
-//   Op::load_vertex_ex(args, gid, own, red)
-template <class Op, class = void>
-struct has_prologue : std::false_type {};
-template <class Op>
-struct has_prologue<Op, std::void_t<decltype(Op::PROLOGUE)>> : std::bool_constant<Op::PROLOGUE> {};
-
-template <class Op>
-__device__ __forceinline__ float4 stage_vertex(const typename Op::Args& a, const LocalVert& v, float& red) {
-  if constexpr (has_prologue<Op>::value) return Op::load_vertex_ex(a, v.gid, v.part < 0, red);
-  else return Op::load_vertex(a, v.gid);
-}
-template <class Op>
-__device__ __forceinline__ float4 own_vertex(const typename Op::Args& a, int gid, float& red) {
-  if constexpr (has_prologue<Op>::value) return Op::load_vertex_ex(a, gid, true, red);
-  else return Op::load_vertex(a, gid);
-}
-
 // the three float4 of one element slot, loaded with streaming (no L1 allocate) loads
 struct PlaneElem {
   float4 a, b, c;
@@ -280,8 +260,8 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile_persistent(Dev
     cp_async_commit();
   } else {
     const int n_lv = s_td[0].n_lv;
-    if (tid < n_lv) vreg0 = stage_vertex<Op>(a, lv_buf(0)[tid], red);
-    if (tid + B < n_lv) vreg1 = stage_vertex<Op>(a, lv_buf(0)[tid + B], red);
+    if (tid < n_lv) vreg0 = Op::load_vertex(a, lv_buf(0)[tid].gid);
+    if (tid + B < n_lv) vreg1 = Op::load_vertex(a, lv_buf(0)[tid + B].gid);
   }
 
   for (int k = 0;; ++k) {
@@ -318,7 +298,7 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile_persistent(Dev
     } else {
       if (tid < td.n_lv) sv[tid] = vreg0;
       if (tid + B < td.n_lv) sv[tid + B] = vreg1;
-      for (int l = tid + 2 * B; l < td.n_lv; l += B) sv[l] = stage_vertex<Op>(a, s_lv[l], red);
+      for (int l = tid + 2 * B; l < td.n_lv; l += B) sv[l] = Op::load_vertex(a, s_lv[l].gid);
     }
     __syncthreads();
 
@@ -349,8 +329,8 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile_persistent(Dev
         for (int l = tid; l < n_lv; l += B) cp_async16(&svn[l], Op::vertex_src(a) + nlv[l].gid);
         cp_async_commit();
       } else {
-        if (tid < n_lv) vreg0 = stage_vertex<Op>(a, nlv[tid], red);
-        if (tid + B < n_lv) vreg1 = stage_vertex<Op>(a, nlv[tid + B], red);
+        if (tid < n_lv) vreg0 = Op::load_vertex(a, nlv[tid].gid);
+        if (tid + B < n_lv) vreg1 = Op::load_vertex(a, nlv[tid + B].gid);
       }
     }
     mbar_wait(&s_bar[2], (uint32_t)(k & 1));
@@ -443,7 +423,7 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile(DevTiling tl, 
   mbar_wait(&s_bar[0], 0);
 
   float red = 0.f;
-  for (int l = threadIdx.x; l < td.n_lv; l += B) sv[l] = stage_vertex<Op>(a, s_lv[l], red);
+  for (int l = threadIdx.x; l < td.n_lv; l += B) sv[l] = Op::load_vertex(a, s_lv[l].gid);
   __syncthreads();
 
   auto one = [&](int e, const typename Op::Elem& d) {
@@ -498,14 +478,25 @@ __global__ void __launch_bounds__(kBoundaryBlock) k_boundary(DevTiling tl, typen
   // from the receive plane they stored into (no unpack kernel).  The sequence bookkeeping runs even when the
   // solver has already converged, so that all ranks keep counting the same exchanges.
   const HaloDev* hd = FUSE ? tl.hd : nullptr;
+  // "late send" arrangement (object.h: peer_pass): the first tl.n_send CTAs of THIS kernel store the shared
+  // vertices' local sums into the neighbours' memory (the tile kernel is complete: stream order); the flags travel
+  // while the other CTAs finish the ordinary boundary vertices, and only CTAs that own a shared vertex wait for them
+  const int n_send = FUSE ? tl.n_send : 0;
+  if ((int)blockIdx.x < n_send) {
+    // (also when the solver has converged: the sequence numbers must keep advancing on every rank)
+    halo_send_cta(hd->pc, hd->n, hd->hb, tl.bptr, Op::partial_buf(a), blockIdx.x, n_send);
+    return;
+  }
+  const unsigned n_recv_ctas = gridDim.x - (unsigned)n_send;
   uint32_t rseq = 0, rparity = 0;
   // list != nullptr: only these boundary vertices (the ones shared with another rank -- every other boundary vertex
   // was finished inside the tile kernel, see itc_arrive); their arrival counters are re-armed by their huge count
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const int bid = (int)blockIdx.x - n_send;
+  const int idx = bid * blockDim.x + threadIdx.x;
   const int b = list ? (idx < n_list ? list[idx] : tl.n_boundary) : idx;
   if (hd) rparity = halo_recv_begin(hd->pc, rseq, b < tl.n_boundary && hd->bhalo[b] >= 0);
   if (Op::early_exit(a)) {
-    if (hd) halo_recv_end(hd->pc, rseq);
+    if (hd) halo_recv_end(hd->pc, rseq, n_recv_ctas);
     return;
   }
   float red = 0.f;
@@ -515,7 +506,7 @@ __global__ void __launch_bounds__(kBoundaryBlock) k_boundary(DevTiling tl, typen
     const int s0 = tl.bptr[b], s1 = tl.bptr[b + 1] - (hk >= 0 ? 1 : 0);
     const int gid = tl.n_interior + b;
     // the vertex operands do not depend on the partial sums: request them first
-    const float4 vtx = own_vertex<Op>(a, gid, red);
+    const float4 vtx = Op::load_vertex(a, gid);
     const float4 pre = Op::pre(a, gid);
     // Launched with programmatic stream serialization: everything above overlaps the tail of the tile
     // kernel; the partial sums it wrote are visible only after this wait (no-op in a plain launch).
@@ -548,9 +539,9 @@ __global__ void __launch_bounds__(kBoundaryBlock) k_boundary(DevTiling tl, typen
   }
   if (Op::REDUCE) {
     const float r = block_sum(red, s_warp);
-    if (threadIdx.x == 0) Op::red_buf(a)[red_base + blockIdx.x] = (double)r;
+    if (threadIdx.x == 0) Op::red_buf(a)[red_base + bid] = (double)r;
   }
-  if (hd) halo_recv_end(hd->pc, rseq);
+  if (hd) halo_recv_end(hd->pc, rseq, n_recv_ctas);
 }
 
 // prefetch helper shared by the Ops: `bytes` per plane starting at slot `slot`
@@ -633,7 +624,8 @@ inline void run_tile_pass(const char* name, const LaunchCfg& c, const DevTiling&
   const int n_bnd = itc ? n_list : tl.n_boundary;
   if (n_bnd > 0 && c.phase != 1) {
     tl.fuse_recv = c.hd ? c.fuse_recv : 0;
-    const int nb = (n_bnd + kBoundaryBlock - 1) / kBoundaryBlock;
+    tl.n_send = (c.hd && c.fuse_recv) ? c.bnd_send : 0;     // late send: sender CTAs at the front of the boundary kernel
+    const int nb = (n_bnd + kBoundaryBlock - 1) / kBoundaryBlock + tl.n_send;
 #if FEMB_PDL
     // programmatic dependent launch: the boundary kernel's CTAs are scheduled while the tile kernel drains
     cudaLaunchConfig_t lc = {};

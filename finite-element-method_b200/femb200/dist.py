@@ -275,7 +275,7 @@ class SlabHalo:
         fixed = (tol == 0.0)
         n_cap = max_iter if max_iter > 0 else (500 if method == 1 else 20000)
         # single-reduction CG (A^T A) sees r.r of update k in iteration k + 1; Jacobi needs 2 more passes (api_solve.cu)
-        n_it = (n_cap + (1 if (preconditioned == 1 and not fixed) else 0)) if method == 1 else n_cap + 2
+        n_it = (n_cap + (1 if (preconditioned == 1 and not fixed) else 0)) if method == 1 else n_cap + 2   # (+1: harmless for the textbook loop)
         handle.solve_begin(dt, method, preconditioned, max_iter, tol)
         self._until_iter(handle)                       # prologue: assemble, A^T b, initial residual
         graph = None

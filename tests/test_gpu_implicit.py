@@ -129,21 +129,50 @@ def test_advect_implicit_parity(case):
     assert rel(h.get(c.F_POS), p) <= 1e-7 and rel(h.get(c.F_VEL), v) <= 2e-6 and rel(h.get(c.F_VEL_G), vg) <= 2e-6
 
 
-def test_implicit_trajectory_cg(case):
-    """C2-style run: implicit CG steps + advect_implicit; positions after the run <= 1e-4."""
+@pytest.mark.parametrize("method,precond", [(1, 1), (1, 0), (0, 0)])
+def test_implicit_trajectory_100_steps(case, method, precond):
+    """C2-style run, north_star's length: 100 x [implicit solve + advect_implicit] with A^T A-CG, plain CG and Jacobi
+    against the dense oracle (the reference's serial sweep for Jacobi); positions after the run <= 1e-4."""
     c, h = case["c"], case["h"]
     dim = case["pos"].shape[1]
-    dt, g_dir, n = 5e-4 if case["name"] != "cube_fine" else 1e-4, [0, -1, 0][:dim], 30
+    dt, g_dir, n = 5e-4 if case["name"] != "cube_fine" else 1e-4, [0, -1, 0][:dim], 100
+    if case["name"] == "cube_multi_tile" and n > 40:
+        n = 40                                      # 216 vertices: the dense oracle costs ~1 s per step
     p, v = case["pos"].copy(), np.zeros_like(case["pos"])
     vg = np.zeros_like(p)
     h.set(c.F_VEL, v)
     past = np.zeros_like(p)
     for _ in range(n):
         v, past, _ = o.implicit_solver_neo_hookean(p, v, case["el"], case["ref"], case["vol"], case["mass"],
-                                                   case["mu"], case["lam"], dt, 1, 1, past)
+                                                   case["mu"], case["lam"], dt, method, precond, past)
         o.advect_implicit(p, v, vg, dt, g_dir, case["mat"]["damping"], [])
-        h.implicit_solve(dt, 1, 1, fetch=False)
+        h.implicit_solve(dt, method, precond, fetch=False)
         h.advect_implicit(dt, g_dir)
     got = h.get(c.F_POS)
     assert rel(got, p) <= 1e-4
     assert rel(got - case["pos"], p - case["pos"]) <= 2e-2
+
+
+def test_single_reduction_cg_matches_textbook_cg(case, monkeypatch):
+    """FEMB_CG_SINGLE_REDUCTION=1 (Chronopoulos-Gear arrangement of the A^T A loop, api_solve.cu; the default on thin
+    multi-GPU slabs): same solution as the textbook loop to the stop tolerance, iteration count within 2."""
+    c, h = case["c"], case["h"]
+    dt = 1e-4 if case["name"] == "cube_fine" else 2e-3       # large dt on the coarse meshes: a dozen iterations
+    res = {}
+    for flag in ("0", "1"):
+        monkeypatch.setenv("FEMB_CG_SINGLE_REDUCTION", flag)
+        h.set(c.F_POS, case["pos"]); h.set(c.F_VEL, case["vel"])
+        it, resid = h.implicit_solve(dt, 1, 1)
+        res[flag] = (it, resid, h.get(c.F_VEC_X))
+        assert resid <= 1e-5 or it == 500
+    assert abs(res["0"][0] - res["1"][0]) <= 2, (res["0"][:2], res["1"][:2])
+    assert rel(res["1"][2], res["0"][2]) <= 2e-3
+    # fixed iteration count (benchmark mode): every scheduled update is applied
+    monkeypatch.setenv("FEMB_CG_SINGLE_REDUCTION", "1")
+    h.set(c.F_POS, case["pos"]); h.set(c.F_VEL, case["vel"])
+    h.implicit_solve(dt, 1, 1, max_iter=3, tol=0.0)
+    x3 = h.get(c.F_VEC_X)
+    monkeypatch.setenv("FEMB_CG_SINGLE_REDUCTION", "0")
+    h.set(c.F_POS, case["pos"]); h.set(c.F_VEL, case["vel"])
+    h.implicit_solve(dt, 1, 1, max_iter=3, tol=0.0)
+    assert rel(x3, h.get(c.F_VEC_X)) <= 1e-4

@@ -164,6 +164,7 @@ def test_implicit_solve_driver_gloo_world2():
     ("peer", {}),                                   # exchange fused into the pass's own kernels (default)
     ("peer", {"FEMB_PEER_FUSED_WAVES": "0"}),       # thick-slab variant: persistent operator kernels + send kernel
     ("peer", {"FEMB_PEER_FUSED": "0"}),             # separate send / receive / reduce kernels
+    ("peer", {"FEMB_PEER_MODE": "late"}),           # one tile kernel; sender CTAs at the front of the boundary kernel
     ("nccl", {}),
 ])
 def test_two_rank_slabs_match_single_gpu(comm, extra):
