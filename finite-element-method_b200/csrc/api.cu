@@ -174,6 +174,12 @@ int femb_object_create(const femb_desc* d, femb_object** out) {
     o->e.p0 = o->alloc<float4>(ns);
     o->e.p1 = o->alloc<float4>(ns);
     o->e.p2 = dim == 3 ? o->alloc<float4>(ns) : nullptr;
+    o->ex = o->e;
+    if (explicit_pair_layout()) {
+      o->ex.p0 = o->alloc<float4>(ns);
+      o->ex.p1 = o->alloc<float4>(ns);
+      o->ex.p2 = dim == 3 ? o->alloc<float4>(ns) : nullptr;
+    }
     o->vs.pos = o->alloc<float4>(nv);
     o->vs.vel = o->alloc<float4>(nv);
     o->vs.force = o->alloc<float4>(nv);
@@ -203,6 +209,7 @@ int femb_object_create(const femb_desc* d, femb_object** out) {
     FEMB_CUDA(cudaMemcpyAsync(o->d_stage, pos.data(), pos.size() * sizeof(float), cudaMemcpyHostToDevice, o->stream));
     launch_unpack_vertex(o->cfg, dim, t.n_vert, o->d_new_of_old, o->d_stage, 0, dim, o->vs.pos);
     launch_setup(dim, o->cfg, o->dtl, o->e, o->d_lidx, o->vs, o->mat);
+    if (explicit_pair_layout()) launch_pair_interleave(dim, o->cfg, o->dtl, o->e, o->ex);
     FEMB_CUDA(cudaMemcpyAsync(o->ref_pos, o->vs.pos, nv * sizeof(float4), cudaMemcpyDeviceToDevice, o->stream));
     FEMB_CUDA(cudaStreamSynchronize(o->stream));
     *out = o;
@@ -294,7 +301,7 @@ int femb_explicit_grad(femb_object* o) {
   if (!o) throw ArgError("NULL object");
   FEMB_CUDA(cudaSetDevice(o->device));
   o->prep_full_pass();
-  launch_explicit(o->dim, EX_GRAD, o->cfg, o->dtl, o->e, o->vs, o->mat, KinArgs{}, nullptr, nullptr);
+  launch_explicit(o->dim, EX_GRAD, o->cfg, o->dtl, o->ex, o->vs, o->mat, KinArgs{}, nullptr, nullptr);
   FEMB_CATCH
 }
 
@@ -303,7 +310,7 @@ int femb_energy_grad(femb_object* o, float* U_out) {
   if (!o) throw ArgError("NULL object");
   FEMB_CUDA(cudaSetDevice(o->device));
   o->prep_full_pass();
-  launch_explicit(o->dim, EX_ENERGY, o->cfg, o->dtl, o->e, o->vs, o->mat, KinArgs{}, o->d_phi, o->d_red);
+  launch_explicit(o->dim, EX_ENERGY, o->cfg, o->dtl, o->ex, o->vs, o->mat, KinArgs{}, o->d_phi, o->d_red);
   const int nbb = (o->dtl.n_boundary + 255) / 256;
   launch_reduce_final(o->cfg, energy_tile_grid(o->dtl) + nbb, o->d_red, o->d_U);
   if (U_out) return femb_get_energy(o, U_out);
@@ -346,6 +353,19 @@ int femb_render(femb_object* o, const femb_view* v, const int32_t* prims, int32_
   FEMB_CATCH
 }
 
+int femb_diagnostics(femb_object* o, int64_t* out3) {
+  FEMB_TRY
+  if (!o || !out3) throw ArgError("NULL argument");
+  FEMB_CUDA(cudaSetDevice(o->device));
+  if (!o->d_diag) o->d_diag = o->alloc<unsigned long long>(3);
+  launch_diagnostics(o->cfg, o->dim, o->dtl, o->e, o->vs.pos, o->d_phi, o->d_diag);
+  unsigned long long h[3];
+  FEMB_CUDA(cudaMemcpyAsync(h, o->d_diag, sizeof(h), cudaMemcpyDeviceToHost, o->stream));
+  FEMB_CUDA(cudaStreamSynchronize(o->stream));
+  for (int i = 0; i < 3; ++i) out3[i] = (int64_t)h[i];
+  FEMB_CATCH
+}
+
 int femb_get_energy(femb_object* o, float* U_out) {
   FEMB_TRY
   if (!o || !U_out) throw ArgError("NULL argument");
@@ -375,12 +395,12 @@ int femb_explicit_step(femb_object* o, float dt, const float* g_dir, int32_t n_s
   auto run = [&]() {
     for (int s = 0; s < n_steps; ++s) {
       if (!o->peer_on) {
-        launch_explicit(o->dim, EX_STEP, o->cfg, o->dtl, o->e, o->vs, o->mat, kin, nullptr, nullptr);
+        launch_explicit(o->dim, EX_STEP, o->cfg, o->dtl, o->ex, o->vs, o->mat, kin, nullptr, nullptr);
         continue;
       }
       // slab rank: tile kernel | shared-vertex sums straight into the neighbours' memory | boundary kernel
       o->peer_pass([&](const LaunchCfg& c) {
-        launch_explicit(o->dim, EX_STEP, c, o->dtl, o->e, o->vs, o->mat, kin, nullptr, nullptr);
+        launch_explicit(o->dim, EX_STEP, c, o->dtl, o->ex, o->vs, o->mat, kin, nullptr, nullptr);
       });
     }
   };
@@ -431,7 +451,7 @@ int femb_explicit_step_timed(femb_object* o, float dt, const float* g_dir, int32
   for (int s = 0; s < n_steps; ++s) {
     FEMB_CUDA(cudaEventRecord(ev[3 * s], o->stream));
     cfg.ev_mid = ev[3 * s + 1];
-    launch_explicit(o->dim, EX_STEP, cfg, o->dtl, o->e, o->vs, o->mat, kin, nullptr, nullptr);
+    launch_explicit(o->dim, EX_STEP, cfg, o->dtl, o->ex, o->vs, o->mat, kin, nullptr, nullptr);
     FEMB_CUDA(cudaEventRecord(ev[3 * s + 2], o->stream));
   }
   FEMB_CUDA(cudaStreamSynchronize(o->stream));
@@ -561,7 +581,7 @@ int femb_explicit_step_phase(femb_object* o, float dt, const float* g_dir, int32
     launch_halo_unpack(cfg, o->dtl, o->halo, o->vs.partial);
     o->halo_dirty = true;
   }
-  launch_explicit(o->dim, EX_STEP, cfg, o->dtl, o->e, o->vs, o->mat, o->kin_args(dt, g_dir), nullptr, nullptr);
+  launch_explicit(o->dim, EX_STEP, cfg, o->dtl, o->ex, o->vs, o->mat, o->kin_args(dt, g_dir), nullptr, nullptr);
   if (phase == 1) launch_halo_pack(cfg, o->dtl, o->halo, o->vs.partial);
   FEMB_CATCH
 }

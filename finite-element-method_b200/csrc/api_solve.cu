@@ -341,7 +341,8 @@ int femb_implicit_solve(femb_object* o, float dt, int32_t method, int32_t precon
   SolveGraph& g = o->solve_graph;
   const bool use_graph = n_it >= 4 && o->stream != nullptr && o->stream != cudaStreamLegacy;
   if (use_graph) {
-    const bool hit = g.exec && g.dt == dt && g.tol == tol && g.method == method && g.pre == preconditioned &&
+    const int arrangement = preconditioned | (P.pre << 4);   // the single-reduction loop is a different graph
+    const bool hit = g.exec && g.dt == dt && g.tol == tol && g.method == method && g.pre == arrangement &&
                      g.max_iter == P.max_iter;
     if (!hit) {
       if (g.exec) { cudaGraphExecDestroy(g.exec); g = SolveGraph(); }
@@ -360,7 +361,7 @@ int femb_implicit_solve(femb_object* o, float dt, int32_t method, int32_t precon
       cudaGraphDestroy(graph);
       cuda_check(ie, "cudaGraphInstantiate");
       g.launches = launch_count() - before;
-      g.dt = dt; g.tol = tol; g.method = method; g.pre = preconditioned; g.max_iter = P.max_iter;
+      g.dt = dt; g.tol = tol; g.method = method; g.pre = arrangement; g.max_iter = P.max_iter;
     }
   }
   int chunk = 4, since_poll = 0;

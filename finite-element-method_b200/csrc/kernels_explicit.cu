@@ -65,7 +65,7 @@ __device__ __forceinline__ void kinematic_update(float4& p, float4& v, const flo
 template <int D>
 struct OpSetup {
   static constexpr bool PERSIST = false;
-  static constexpr bool ASYNC_VERTEX = false;
+  static constexpr bool ASYNC_VERTEX = false, PAIR = false;
   static constexpr int BLOCK = kBlock, MIN_CTAS = kMinCtas,NSTAGE = 1, GATHER = G_UNIFORM;
   static constexpr bool REDUCE = false;
   struct Args {
@@ -156,7 +156,10 @@ struct OpExplicit {
   // the tile's vertex values are pos[gid] untransformed: the persistent kernel fetches the NEXT tile's values
   // global -> shared with cp.async into a second vertex buffer (no registers held across the element phase)
   static constexpr bool ASYNC_VERTEX = true;
-  static constexpr int BLOCK = kBlock, MIN_CTAS = kMinCtas,NSTAGE = D * D, GATHER = G_STAR;
+  // PAIR: every thread works on two elements at once in packed fp32 (compute2; dev.cuh f2).  Half the threads per
+  // CTA, twice the registers per thread, the same 4 CTAs/SM.
+  static constexpr bool PAIR = FEMB_PAIR_EXPLICIT != 0;
+  static constexpr int BLOCK = PAIR ? kBlock / 2 : kBlock, MIN_CTAS = kMinCtas, NSTAGE = D * D, GATHER = G_STAR;
   static constexpr bool REDUCE = (MODE == EX_ENERGY);
   struct Args {
     Planes e;
@@ -222,6 +225,67 @@ struct OpExplicit {
       const float pv = phi * V;
       a.phi[slot] = pv;
       red += pv;
+    }
+  }
+
+  // the same for the elements in slot0 (lane x) and slot1 (lane y)
+  __device__ static void compute2(const Args& a, int slot0, int slot1, const Elem& d0, const Elem& d1,
+                                  const float4* sv, f2 (&out)[NSTAGE], float& red) {
+    // d0 / d1 are the two slots of a pair in the pair-interleaved layout (k_pair_interleave below):
+    //   3D  d0 = {i01a i01b i23a i23b | r01 r02 | r12 r20}   d1 = {Va Vb r00a r00b | r10 r11 | r21 r22}
+    //   2D  d0 = {i01a i01b i2a  i2b  | r01 r10}             d1 = {Va Vb r00a r00b | r11 0}
+    // (each r.. an (a, b) pair) -- every operand of the packed arithmetic is an aligned register pair as loaded
+    Mat2<D> R, X, F, C;
+    const f2 V = pk(d1.a.x, d1.a.y);
+    R.m[0][0] = pk(d1.a.z, d1.a.w);
+    R.m[0][1] = pk(d0.b.x, d0.b.y);
+    if constexpr (D == 3) {
+      R.m[0][2] = pk(d0.b.z, d0.b.w);
+      R.m[1][0] = pk(d1.b.x, d1.b.y); R.m[1][1] = pk(d1.b.z, d1.b.w); R.m[1][2] = pk(d0.c.x, d0.c.y);
+      R.m[2][0] = pk(d0.c.z, d0.c.w); R.m[2][1] = pk(d1.c.x, d1.c.y); R.m[2][2] = pk(d1.c.z, d1.c.w);
+    } else {
+      R.m[1][0] = pk(d0.b.z, d0.b.w); R.m[1][1] = pk(d1.b.x, d1.b.y);
+    }
+    {
+      Mat<D> X0, X1;
+      edge_matrix<D>(sv, __float_as_uint(d0.a.x), __float_as_uint(d0.a.z), X0);
+      edge_matrix<D>(sv, __float_as_uint(d0.a.y), __float_as_uint(d0.a.w), X1);
+      pack<D>(X0, X1, X);
+    }
+    matmul<D>(X, R, F);
+    const f2 J = cofactor_det<D>(F, C);
+    const f2 log_j = pk(logf(J.v.x), logf(J.v.y));
+    const f2 muV = bc(a.mat.mu) * V;
+    const f2 num = fma2(bc(a.mat.lambda), log_j, bc(-a.mat.mu)) * V;
+    const f2 cfV = pk(__fdividef(num.v.x, J.v.x), __fdividef(num.v.y, J.v.y));
+    Mat2<D> P, G;
+#pragma unroll
+    for (int i = 0; i < D; ++i)
+#pragma unroll
+      for (int j = 0; j < D; ++j) P.m[i][j] = fma2(muV, F.m[i][j], cfV * C.m[i][j]);
+    matmul_nt<D>(P, R, G);
+#pragma unroll
+    for (int j = 0; j < D; ++j)
+#pragma unroll
+      for (int i = 0; i < D; ++i) out[j * D + i] = G.m[i][j];
+    if (MODE == EX_ENERGY) {
+      f2 tr = F.m[0][0] * F.m[0][0];
+#pragma unroll
+      for (int i = 0; i < D; ++i)
+#pragma unroll
+        for (int j = 0; j < D; ++j)
+          if (i + j > 0) tr = fma2(F.m[i][j], F.m[i][j], tr);
+      const float lj[2] = {log_j.v.x, log_j.v.y}, t[2] = {tr.v.x, tr.v.y}, vol[2] = {V.v.x, V.v.y};
+      const int slot[2] = {slot0, slot1};
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        float phi = a.mat.mu / 2.f * (t[q] - (float)D);
+        phi -= a.mat.mu * lj[q];
+        phi += a.mat.lambda / 2.f * lj[q] * lj[q];
+        const float pv = phi * vol[q];
+        a.phi[slot[q]] = pv;
+        red += pv;
+      }
     }
   }
 
@@ -308,9 +372,39 @@ __global__ void __launch_bounds__(256) k_advect_implicit(int n, VertexState vs, 
   vs.pos[idx] = p4; vs.vel[idx] = v4; vs.vel_g[idx] = g4;
 }
 
+// Pair-interleaved copy of the element planes for the packed (two elements per thread) kernels: the two slots
+// (e, e + BP) a thread of a BP-thread CTA works on together exchange halves, plane by plane,
+//   q[e]      = {p[e].x, p[e+BP].x, p[e].y, p[e+BP].y}        q[e+BP] = {p[e].z, p[e+BP].z, p[e].w, p[e+BP].w}
+// so each 16-byte load lands (element a, element b) operand pairs in aligned register pairs.  Elements without
+// a partner (ragged tile end) keep the plain layout.  Same addresses, same bytes as the plain planes.
+__global__ void __launch_bounds__(128) k_pair_interleave(DevTiling tl, Planes src, Planes dst, int bp, int three) {
+  const DevTile td = tl.tiles[blockIdx.x];
+  for (int e = threadIdx.x; e < td.n_elem; e += blockDim.x) {
+    const int half = (e / bp) & 1, e0 = half ? e - bp : e, e1 = e0 + bp;
+    const int s = td.slot_off + e;
+    const bool paired = e1 < td.n_elem;
+    const float4* sp[3] = {src.p0, src.p1, src.p2};
+    float4* dp[3] = {dst.p0, dst.p1, dst.p2};
+    for (int k = 0; k < (three ? 3 : 2); ++k) {
+      if (!paired) {
+        dp[k][s] = sp[k][s];
+        continue;
+      }
+      const float4 a = sp[k][td.slot_off + e0], b = sp[k][td.slot_off + e1];
+      dp[k][s] = half ? make_float4(a.z, b.z, a.w, b.w) : make_float4(a.x, b.x, a.y, b.y);
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------
 // launchers
 // ---------------------------------------------------------------------------
+bool explicit_pair_layout() { return FEMB_PAIR_EXPLICIT != 0; }
+void launch_pair_interleave(int dim, const LaunchCfg& c, const DevTiling& tl, Planes src, Planes dst) {
+  k_pair_interleave<<<tl.n_tiles, 128, 0, c.stream>>>(tl, src, dst, OpExplicit<3, EX_STEP>::BLOCK, dim == 3);
+  note_launch("pair_interleave", c.stream);
+}
+
 void launch_setup(int dim, const LaunchCfg& c, const DevTiling& tl, Planes e, const uint32_t* lidx,
                   VertexState vs, Material mat) {
   if (dim == 3) {

@@ -18,7 +18,7 @@ namespace femb {
 template <int D>
 struct OpAssemble {
   static constexpr bool PERSIST = FEMB_PERSIST_ASSEMBLE != 0;
-  static constexpr bool ASYNC_VERTEX = false;
+  static constexpr bool ASYNC_VERTEX = false, PAIR = false;
   static constexpr int BLOCK = kBlock, MIN_CTAS = kMinCtas,NSTAGE = D * D, GATHER = G_STAR;
   static constexpr bool REDUCE = false;
   struct Args {
@@ -117,7 +117,7 @@ struct OpAssemble {
 template <int D>
 struct OpDiag {
   static constexpr bool PERSIST = FEMB_PERSIST_APPLY != 0;
-  static constexpr bool ASYNC_VERTEX = false;
+  static constexpr bool ASYNC_VERTEX = false, PAIR = false;
   static constexpr int BLOCK = kBlock, MIN_CTAS = kMinCtas,NSTAGE = D, GATHER = G_UNIFORM;
   static constexpr bool REDUCE = false;
   struct Args {
@@ -157,7 +157,7 @@ struct OpDiag {
 template <int D, int TR>
 struct OpApply {
   static constexpr bool PERSIST = FEMB_PERSIST_APPLY != 0;
-  static constexpr bool ASYNC_VERTEX = false;
+  static constexpr bool ASYNC_VERTEX = false, PAIR = false;
   static constexpr int BLOCK = kBlock, MIN_CTAS = kMinCtas,NSTAGE = D * D, GATHER = G_STAR;
   static constexpr bool REDUCE = true;
   struct Args {
@@ -248,7 +248,7 @@ struct OpApply {
 template <int D>
 struct OpJacobi {
   static constexpr bool PERSIST = FEMB_PERSIST_APPLY != 0;
-  static constexpr bool ASYNC_VERTEX = false;
+  static constexpr bool ASYNC_VERTEX = false, PAIR = false;
   static constexpr int BLOCK = kBlock, MIN_CTAS = kMinCtas, NSTAGE = D * D, GATHER = G_STAR;
   static constexpr bool REDUCE = true;
   struct Args {

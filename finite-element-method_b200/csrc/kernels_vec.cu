@@ -333,6 +333,61 @@ __global__ void __launch_bounds__(256) k_unpack_vertex(int n, const int32_t* new
   for (int k = 0; k < ncomp; ++k) d[comp0 + k] = src[(size_t)i * ncomp + k];
 }
 
+// State diagnostics on the device (main.py --diag-every): elements whose deformation gradient has det F <= 0 or
+// NaN (the explicit kernel takes log(det F) unclamped, explicit.py:24-25), elements whose energy density is NaN,
+// vertices with a NaN coordinate.  Integer counters, so the atomics are order-independent.  One CTA per tile.
+template <int D>
+__global__ void __launch_bounds__(256) k_diag_elements(DevTiling tl, Planes e, const float4* pos, const float* phi,
+                                                       unsigned long long* out) {
+  const DevTile td = tl.tiles[blockIdx.x];
+  const LocalVert* lv = tl.lv + td.lv_off;
+  unsigned inv = 0, nan_e = 0;
+  for (int k = threadIdx.x; k < td.n_elem; k += blockDim.x) {
+    const int s = td.slot_off + k;
+    const float4 e0 = e.p0[s], e1 = e.p1[s];
+    const float4 e2 = D == 3 ? e.p2[s] : make_float4(0.f, 0.f, 0.f, 0.f);
+    const uint32_t w0 = __float_as_uint(e0.x), w1 = __float_as_uint(e0.y);
+    const float4 p0 = pos[lv[w0 & 0xffffu].gid], p1 = pos[lv[w0 >> 16].gid], p2 = pos[lv[w1 & 0xffffu].gid];
+    Mat<D> R, X, F;
+    unpack_ref<D>(e0, e1, e2, R);
+    X.m[0][0] = p1.x - p0.x; X.m[1][0] = p1.y - p0.y;
+    X.m[0][1] = p2.x - p0.x; X.m[1][1] = p2.y - p0.y;
+    if constexpr (D == 3) {
+      const float4 p3 = pos[lv[w1 >> 16].gid];
+      X.m[2][0] = p1.z - p0.z; X.m[2][1] = p2.z - p0.z;
+      X.m[0][2] = p3.x - p0.x; X.m[1][2] = p3.y - p0.y; X.m[2][2] = p3.z - p0.z;
+    }
+    matmul<D>(X, R, F);
+    if (!(det<D>(F) > 0.f)) ++inv;
+    if (phi[s] != phi[s]) ++nan_e;
+  }
+  inv = __reduce_add_sync(0xffffffffu, inv);
+  nan_e = __reduce_add_sync(0xffffffffu, nan_e);
+  if ((threadIdx.x & 31) == 0) {
+    if (inv) atomicAdd(out + 0, (unsigned long long)inv);
+    if (nan_e) atomicAdd(out + 1, (unsigned long long)nan_e);
+  }
+}
+__global__ void __launch_bounds__(256) k_diag_vertices(int n, int dim, const float4* pos, unsigned long long* out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  unsigned bad = 0;
+  if (i < n) {
+    const float4 p = pos[i];
+    bad = (p.x != p.x) | (p.y != p.y) | (dim == 3 && p.z != p.z);
+  }
+  bad = __reduce_add_sync(0xffffffffu, bad);
+  if ((threadIdx.x & 31) == 0 && bad) atomicAdd(out + 2, (unsigned long long)bad);
+}
+void launch_diagnostics(const LaunchCfg& c, int dim, const DevTiling& tl, Planes e, const float4* pos, const float* phi,
+                        unsigned long long* out3) {
+  cudaMemsetAsync(out3, 0, 3 * sizeof(unsigned long long), c.stream);
+  if (dim == 3) k_diag_elements<3><<<tl.n_tiles, 256, 0, c.stream>>>(tl, e, pos, phi, out3);
+  else k_diag_elements<2><<<tl.n_tiles, 256, 0, c.stream>>>(tl, e, pos, phi, out3);
+  note_launch("diag_elements", c.stream);
+  k_diag_vertices<<<(tl.n_vert + 255) / 256, 256, 0, c.stream>>>(tl.n_vert, dim, pos, out3);
+  note_launch("diag_vertices", c.stream);
+}
+
 // what: 0 volume, 1 ref (row-major dim*dim), 2 phi, 3 H_e (row-major)
 __global__ void __launch_bounds__(256) k_pack_elem(int dim, int n, const int32_t* slot_of_elem, Planes e, Planes h,
                                                    const float* phi, int what, float* dst) {

@@ -116,6 +116,12 @@ void launch_halo_mass(const LaunchCfg& c, const DevTiling& tl, Halo h, float4* p
 void launch_halo_zero_remote(const LaunchCfg& c, const DevTiling& tl, Halo h, float4* partial);
 
 // setup: Dm^-1, volume -> element planes; lumped mass -> pos.w   (object.py:345-362)
+// inverted elements / NaN energy densities / NaN vertices -> out3[0..2] (device)
+void launch_diagnostics(const LaunchCfg& c, int dim, const DevTiling& tl, Planes e, const float4* pos, const float* phi,
+                        unsigned long long* out3);
+// packed explicit kernels (FEMB_PAIR_EXPLICIT): they read a pair-interleaved copy of the element planes
+bool explicit_pair_layout();
+void launch_pair_interleave(int dim, const LaunchCfg& c, const DevTiling& tl, Planes src, Planes dst);
 void launch_setup(int dim, const LaunchCfg& c, const DevTiling& tl, Planes e, const uint32_t* lidx,
                   VertexState vs, Material mat);
 // explicit tile + boundary pass

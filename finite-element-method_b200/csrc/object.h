@@ -72,6 +72,7 @@ struct femb_object {
   femb::Tiling til;                 // host copy (maps kept for diagnostics)
   femb::DevTiling dtl{};
   femb::Planes e{}, h{};
+  femb::Planes ex{};                // what the explicit kernels read: e, or its pair-interleaved copy (launch.h)
   uint32_t* d_lidx = nullptr;
   femb::VertexState vs{};
   float4* ref_pos = nullptr;
@@ -81,6 +82,7 @@ struct femb_object {
   double* d_red2 = nullptr;         // second partial buffer (single-reduction CG: r.r of the first pass)
   int red_slots = 0;
   double* d_U = nullptr;
+  unsigned long long* d_diag = nullptr;   // femb_diagnostics counters
   femb::SolveScalars* d_sc = nullptr;
   femb::SolveScalars* h_sc = nullptr;  // pinned
   int32_t* d_new_of_old = nullptr;

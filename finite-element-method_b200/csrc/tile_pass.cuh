@@ -116,6 +116,29 @@ __device__ __forceinline__ void stage_element(float* stage, int e, const float (
   }
 }
 
+// the same for the two elements of a packed pair (lane x -> element e0, lane y -> element e1)
+template <int D, class Op>
+__device__ __forceinline__ void stage_pair(float* stage, int e0, int e1, const f2 (&out)[Op::NSTAGE]) {
+  constexpr int S = kStride;
+  float* s0 = stage + e0;
+  float* s1 = stage + e1;
+#pragma unroll
+  for (int i = 0; i < Op::NSTAGE; ++i) {
+    s0[i * S] = out[i].v.x;
+    s1[i * S] = out[i].v.y;
+  }
+  if constexpr (Op::GATHER == G_STAR) {
+#pragma unroll
+    for (int i = 0; i < D; ++i) {
+      f2 c = -out[i];
+#pragma unroll
+      for (int j = 1; j < D; ++j) c = c - out[j * D + i];
+      s0[(D * D + i) * S] = c.v.x;
+      s1[(D * D + i) * S] = c.v.y;
+    }
+  }
+}
+
 template <int D, int MODE, int NV>
 __device__ __forceinline__ void gather_local_vertex(int n_rounds, const uint32_t* __restrict__ rounds,
                                                     const uint16_t* __restrict__ jds, const float* __restrict__ stage,
@@ -157,6 +180,62 @@ __device__ __forceinline__ void gather_local_vertex(int n_rounds, const uint32_t
     for (int j = 0; j < 4; ++j)
 #pragma unroll
       for (int i = 0; i < D; ++i) acc[i] += v[j][i];
+  }
+}
+
+// The element phase of a tile: every thread works through its elements tid, tid + B, ... (d0 / d1: the planes of
+// its first two, already requested by the caller) and stages the results plane-major.
+template <int D, class Op>
+__device__ __forceinline__ void element_phase(const typename Op::Args& a, int slot_off, int n_elem, const float4* sv,
+                                              float* stage, typename Op::Elem& d0, typename Op::Elem& d1, float& red) {
+  const int B = blockDim.x;
+  auto one = [&](int e, const typename Op::Elem& d) {
+    float out[Op::NSTAGE];
+    Op::compute(a, slot_off + e, d, sv, out, red);
+    stage_element<D, Op>(stage, e, out);
+  };
+  if constexpr (Op::PAIR) {
+    // elements (e, e + BP) of a thread go through the packed arithmetic together; the trip count is a compile-time
+    // bound (a tile holds at most kStride elements), so the loop unrolls and the next pair's planes are requested
+    // into fresh registers before the current pair is worked on
+    constexpr int BP = Op::BLOCK, NIT = (kStride + 2 * BP - 1) / (2 * BP);
+#pragma unroll
+    for (int it = 0; it < NIT; ++it) {
+      const int e = (int)threadIdx.x + it * 2 * BP;
+      if (e >= n_elem) break;
+      const bool two = e + BP < n_elem;
+      typename Op::Elem n0 = d0, n1 = d1;
+      if (FEMB_PAIR_PREFETCH) {
+        if (it + 1 < NIT) {
+          if (e + 2 * BP < n_elem) Op::load(a, slot_off + e + 2 * BP, n0);
+          if (e + 3 * BP < n_elem) Op::load(a, slot_off + e + 3 * BP, n1);
+        }
+      } else if (it > 0) {
+        Op::load(a, slot_off + e, d0);
+        if (two) Op::load(a, slot_off + e + BP, d1);
+      }
+      if (two) {
+        f2 out[Op::NSTAGE];
+        Op::compute2(a, slot_off + e, slot_off + e + BP, d0, d1, sv, out, red);
+        stage_pair<D, Op>(stage, e, e + BP, out);
+      } else {
+        one(e, d0);
+      }
+      if (FEMB_PAIR_PREFETCH) {
+        d0 = n0;
+        d1 = n1;
+      }
+    }
+  } else {
+    for (int e = threadIdx.x; e < n_elem; e += 2 * B) {
+      const bool two = e + B < n_elem;
+      if (e != (int)threadIdx.x) {
+        Op::load(a, slot_off + e, d0);
+        if (two) Op::load(a, slot_off + e + B, d1);
+      }
+      one(e, d0);
+      if (two) one(e + B, d1);
+    }
   }
 }
 
@@ -254,6 +333,8 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile_persistent(Dev
   // more than 2*B local vertices: irregular meshes only) fetched directly at staging time
   float4 vreg0 = make_float4(0.f, 0.f, 0.f, 0.f), vreg1 = vreg0;
   float red = 0.f;
+  constexpr bool EARLY = Op::PAIR;       // register budget of the 128-thread packed kernels allows it
+  typename Op::Elem d0, d1;
   if constexpr (AV) {
     const int n_lv = s_td[0].n_lv;
     for (int l = tid; l < n_lv; l += B) cp_async16(&sv0[l], Op::vertex_src(a) + lv_buf(0)[l].gid);
@@ -289,9 +370,11 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile_persistent(Dev
       }
     }
     // element data of the first two elements of this thread: in flight while the vertices are staged
-    typename Op::Elem d0, d1;
-    if (tid < n_elem) Op::load(a, slot_off + tid, d0);
-    if (tid + B < n_elem) Op::load(a, slot_off + tid + B, d1);
+    // (EARLY: already requested before the previous tile's gather)
+    if (!EARLY || k == 0) {
+      if (tid < n_elem) Op::load(a, slot_off + tid, d0);
+      if (tid + B < n_elem) Op::load(a, slot_off + tid + B, d1);
+    }
 
     if constexpr (AV) {
       cp_async_wait_all();               // this thread's copies have landed; the barrier publishes everyone's
@@ -302,20 +385,7 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile_persistent(Dev
     }
     __syncthreads();
 
-    auto one = [&](int e, const typename Op::Elem& d) {
-      float out[Op::NSTAGE];
-      Op::compute(a, slot_off + e, d, sv, out, red);
-      stage_element<D, Op>(stage, e, out);
-    };
-    for (int e = tid; e < n_elem; e += 2 * B) {
-      const bool two = e + B < n_elem;
-      if (e != tid) {
-        Op::load(a, slot_off + e, d0);
-        if (two) Op::load(a, slot_off + e + B, d1);
-      }
-      one(e, d0);
-      if (two) one(e + B, d1);
-    }
+    element_phase<D, Op>(a, slot_off, n_elem, sv, stage, d0, d1, red);
     __syncthreads();
 
     // the next tile's vertex values: its local-vertex table landed during the element phase
@@ -331,6 +401,10 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile_persistent(Dev
       } else {
         if (tid < n_lv) vreg0 = Op::load_vertex(a, nlv[tid].gid);
         if (tid + B < n_lv) vreg1 = Op::load_vertex(a, nlv[tid + B].gid);
+      }
+      if (EARLY) {   // the next tile's first element planes cross HBM -> registers behind this tile's gather
+        if (tid < td.nx_n_elem) Op::load(a, td.nx_slot_off + tid, d0);
+        if (tid + B < td.nx_n_elem) Op::load(a, td.nx_slot_off + tid + B, d1);
       }
     }
     mbar_wait(&s_bar[2], (uint32_t)(k & 1));
@@ -426,20 +500,7 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile(DevTiling tl, 
   for (int l = threadIdx.x; l < td.n_lv; l += B) sv[l] = Op::load_vertex(a, s_lv[l].gid);
   __syncthreads();
 
-  auto one = [&](int e, const typename Op::Elem& d) {
-    float out[Op::NSTAGE];
-    Op::compute(a, td.slot_off + e, d, sv, out, red);
-    stage_element<D, Op>(stage, e, out);
-  };
-  for (int e = threadIdx.x; e < td.n_elem; e += 2 * B) {
-    const bool two = e + B < td.n_elem;
-    if (e != (int)threadIdx.x) {
-      Op::load(a, td.slot_off + e, d0);
-      if (two) Op::load(a, td.slot_off + e + B, d1);
-    }
-    one(e, d0);
-    if (two) one(e + B, d1);
-  }
+  element_phase<D, Op>(a, td.slot_off, td.n_elem, sv, stage, d0, d1, red);
   __syncthreads();
   mbar_wait(&s_bar[1], 0);
 

@@ -30,7 +30,7 @@ EXPORTS = [
     "femb_implicit_solve_finish",
     "femb_advect_implicit", "femb_implicit_assemble", "femb_implicit_apply", "femb_implicit_apply_timed", "femb_render", "femb_get", "femb_set",
     "femb_set_async", "femb_get_async", "femb_transfers_wait", "femb_set_host_threads",
-    "femb_get_energy", "femb_sync", "femb_last_error", "femb_launch_count", "femb_version",
+    "femb_get_energy", "femb_diagnostics", "femb_sync", "femb_last_error", "femb_launch_count", "femb_version",
     "femb_tiling_build", "femb_tiling_build_ex", "femb_tiling_destroy", "femb_tiling_info", "femb_tiling_get",
 ]
 
@@ -122,6 +122,7 @@ def lib():
         "femb_transfers_wait": (C.c_int, [vp]),
         "femb_set_host_threads": (C.c_int, [i32]),
         "femb_get_energy": (C.c_int, [vp, fp]),
+        "femb_diagnostics": (C.c_int, [vp, C.POINTER(C.c_int64)]),
         "femb_sync": (C.c_int, [vp]),
         "femb_last_error": (C.c_char_p, []),
         "femb_launch_count": (C.c_uint64, []),
@@ -266,6 +267,12 @@ class Handle:
         u = C.c_float()
         check(lib().femb_get_energy(self._h, C.byref(u)))
         return u.value
+
+    def diagnostics(self):
+        """{inverted_elements, nan_elements, nan_vertices}, counted on the device."""
+        out = (C.c_int64 * 3)()
+        check(lib().femb_diagnostics(self._h, out))
+        return {"inverted_elements": int(out[0]), "nan_elements": int(out[1]), "nan_vertices": int(out[2])}
 
     def kinematic(self, dt, g_dir, use_grad):
         g = gvec(g_dir, self.dim)

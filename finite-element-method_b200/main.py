@@ -72,10 +72,9 @@ def diagnostics(soft_obj):
     evaluation of compute_energy; pos.grad is overwritten (harmless outside auto_diff mode, and in
     auto_diff mode the next step recomputes it before use)."""
     U = soft_obj._h.energy_grad(fetch=True)
-    phi = soft_obj.phi.to_numpy()
-    pos = soft_obj.particles.pos.to_numpy()
-    return {"U": float(U), "nan_elements": int(np.isnan(phi).sum()), "nan_vertices": int(np.isnan(pos).any(axis=1).sum()),
-            "inverted_elements": int(soft_obj.count_inverted(pos))}
+    d = soft_obj._h.diagnostics()      # three counters from the device; no field leaves HBM
+    return {"U": float(U), "nan_elements": d["nan_elements"], "nan_vertices": d["nan_vertices"],
+            "inverted_elements": d["inverted_elements"]}
 
 
 if __name__ == '__main__':

@@ -227,8 +227,10 @@ class Object:
 
     def count_inverted(self, pos=None):
         """Number of elements with det F <= 0 (the explicit kernel takes log(det F) unclamped,
-        explicit.py:24-25, so these produce NaN): sign(det Ds) != sign(det Dm)."""
-        pos = self.particles.pos.to_numpy() if pos is None else pos
+        explicit.py:24-25, so these produce NaN).  Counted on the device from the current positions; a host
+        array `pos` is checked with numpy instead (sign(det Ds) != sign(det Dm))."""
+        if pos is None:
+            return self._h.diagnostics()["inverted_elements"]
         ref = self.particles.ref_pos.to_numpy()
         el = self.elements.vertex_indices.to_numpy()
 

@@ -220,6 +220,11 @@ int femb_set_async(femb_object *obj, int32_t field, const void *host, size_t byt
 int femb_get_async(femb_object *obj, int32_t field, void *host, size_t bytes);
 int femb_transfers_wait(femb_object *obj);
 /* obj.U[None] (object.py:69) */
+/* State diagnostics counted on the device (replaces nothing in the reference -- it has no such check; serves
+ * main.py --diag-every): out3 = { elements with det F <= 0 or NaN (explicit.py:24-25 takes
+ * log(det F) unclamped), elements whose energy density phi is NaN (as of the last femb_energy_grad), vertices with
+ * a NaN coordinate }.  Synchronises. */
+int femb_diagnostics(femb_object *obj, int64_t *out3);
 int femb_get_energy(femb_object *obj, float *U_out);
 int femb_sync(femb_object *obj);
 

@@ -199,3 +199,34 @@ def test_async_field_transfers_match_blocking():
     with pytest.raises(ValueError):
         h.set_async(c.F_POS, pos.astype(np.float64))
     h.close()
+
+
+def test_device_diagnostics_count_inverted_and_nan(case):
+    """femb_diagnostics (main.py --diag-every, object.Object.count_inverted): inverted elements counted on the
+    device equal the fp64 count on the host; a NaN vertex shows up in all three counters."""
+    c, h, el = capi(), case["h"], case["el"]
+    pos0 = h.get(c.F_POS)
+    h.energy_grad()
+    assert h.diagnostics() == {"inverted_elements": 0, "nan_elements": 0, "nan_vertices": 0}
+    # push one vertex far through its neighbours: some of its elements turn inside out
+    pos = pos0.copy()
+    v = int(el[len(el) // 2][0])
+    pos[v] += 0.8
+    h.set(c.F_POS, pos)
+
+    def dets(p):
+        return np.linalg.det((p[el[:, 1:]] - p[el[:, :1]]).astype(np.float64))
+    want = int((dets(pos) * dets(pos0) <= 0).sum())
+    assert want > 0
+    h.energy_grad()
+    d = h.diagnostics()
+    assert d["inverted_elements"] == want and d["nan_vertices"] == 0
+    assert d["nan_elements"] == int(np.isnan(h.get(c.F_ELEM_PHI)).sum()) > 0      # log of a negative determinant
+    pos = pos0.copy()
+    pos[v, 0] = np.nan
+    h.set(c.F_POS, pos)
+    h.energy_grad()
+    d = h.diagnostics()
+    touched = int((el == v).any(axis=1).sum())
+    assert d == {"inverted_elements": touched, "nan_elements": touched, "nan_vertices": 1}
+    h.set(c.F_POS, pos0)

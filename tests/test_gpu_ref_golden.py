@@ -113,8 +113,9 @@ def test_cuda_path_matches_reference_fixture(name):
         tol = POS_TOL
         if name == "c1_blocks" and step > 1250:
             # after the body has wrapped round the blocks the contact branch makes the trajectory chaotic: two fp32
-            # evaluations that agree to 1e-7 per step part by 6.6e-4 at step 1 500 (round-1 oracle vs reference)
-            tol = 5e-3
+            # evaluations that agree to 1e-7 per step part by 6.6e-4 at step 1 500 (round-1 oracle vs reference);
+            # the packed-pair build of the element kernel (other rounding, 1e-5 at step 1 250) reaches 7.2e-3
+            tol = 2e-2
         report["pos@%d" % step] = rel(out["pos"][k], fx["s_pos"][k])
         assert report["pos@%d" % step] <= tol, (name, step, report)
     if mode == "implicit":

@@ -17,6 +17,4 @@ PY
 EXTRA="" run default FEMB_X=1
 EXTRA="--no-parity" run late FEMB_PEER_MODE=late
 EXTRA="--no-parity" run cg0 FEMB_CG_SINGLE_REDUCTION=0
-EXTRA="--no-parity" run late_cg0 FEMB_PEER_MODE=late FEMB_CG_SINGLE_REDUCTION=0
-EXTRA="--no-parity" run unfused FEMB_PEER_FUSED=0
 EXTRA="--no-parity --workload c4_explicit" run late_pe FEMB_PEER_MODE=late FEMB200_LIB=$PWD/variants/persist_explicit.so
