@@ -353,6 +353,39 @@ int femb_render(femb_object* o, const femb_view* v, const int32_t* prims, int32_
   FEMB_CATCH
 }
 
+int femb_trace_enable(femb_object* o, int32_t on) {
+  FEMB_TRY
+  if (!o) throw ArgError("NULL object");
+  FEMB_CUDA(cudaSetDevice(o->device));
+  FEMB_CUDA(cudaStreamSynchronize(o->stream));
+  // cached graphs carry the trace pointers of the launches they were captured from
+  if (o->graph.exec) { cudaGraphExecDestroy(o->graph.exec); o->graph = StepGraph(); }
+  if (o->solve_graph.exec) { cudaGraphExecDestroy(o->solve_graph.exec); o->solve_graph = SolveGraph(); }
+  const size_t words = (size_t)kTraceSlots * kTraceWords;
+  if (on && !o->d_trace) o->d_trace = o->alloc<unsigned long long>(words);
+  if (on) FEMB_CUDA(cudaMemsetAsync(o->d_trace, 0, words * sizeof(unsigned long long), o->stream));
+  o->cfg.trace = on ? o->d_trace : nullptr;
+  trace_restart();
+  FEMB_CATCH
+}
+
+int femb_trace_get(femb_object* o, uint64_t* words, int32_t max_slots, int32_t* n_out, char* names, size_t names_bytes) {
+  FEMB_TRY
+  if (!o || !words || !n_out) throw ArgError("NULL argument");
+  if (!o->d_trace) throw StateError("femb_trace_get: tracing was never enabled");
+  FEMB_CUDA(cudaSetDevice(o->device));
+  FEMB_CUDA(cudaStreamSynchronize(o->stream));
+  const int n = std::min((int)max_slots, trace_slots_used());
+  FEMB_CUDA(cudaMemcpy(words, o->d_trace, (size_t)n * kTraceWords * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+  *n_out = n;
+  if (names && names_bytes) {
+    std::string all;
+    for (int i = 0; i < n; ++i) { all += trace_slot_name(i); all += '\n'; }
+    std::snprintf(names, names_bytes, "%s", all.c_str());
+  }
+  FEMB_CATCH
+}
+
 int femb_diagnostics(femb_object* o, int64_t* out3) {
   FEMB_TRY
   if (!o || !out3) throw ArgError("NULL argument");
@@ -528,14 +561,26 @@ int femb_peer_bind(femb_object* o, const femb_peer_desc* d) {
     for (size_t k = 0; k < o->til.halo_b.size(); ++k) bhalo[(size_t)o->til.halo_b[k]] = (int32_t)k;
     int32_t* d_bhalo = o->alloc<int32_t>(bhalo.size(), false);
     FEMB_CUDA(cudaMemcpyAsync(d_bhalo, bhalo.data(), bhalo.size() * sizeof(int32_t), cudaMemcpyHostToDevice, o->stream));
-    HaloDev hd{pc, o->halo.n, o->halo.b, d_bhalo};
+    // local partial slots of every shared vertex (its last slot is the remote one)
+    std::vector<int2> hrange(o->til.halo_b.size());
+    for (size_t k = 0; k < hrange.size(); ++k) {
+      const int32_t b = o->til.halo_b[k];
+      hrange[k] = make_int2(o->til.bptr[(size_t)b], o->til.bptr[(size_t)b + 1] - 1);
+    }
+    int2* d_hrange = o->alloc<int2>(hrange.size(), false);
+    FEMB_CUDA(cudaMemcpyAsync(d_hrange, hrange.data(), hrange.size() * sizeof(int2), cudaMemcpyHostToDevice, o->stream));
+    HaloDev hd{pc, o->halo.n, o->halo.b, d_hrange, d_bhalo};
     HaloDev* d_hd = o->alloc<HaloDev>(1, false);
     FEMB_CUDA(cudaMemcpyAsync(d_hd, &hd, sizeof(HaloDev), cudaMemcpyHostToDevice, o->stream));
     FEMB_CUDA(cudaStreamSynchronize(o->stream));   // bhalo / hd are stack / local storage
     o->d_halo_dev = fused ? d_hd : nullptr;
-    o->n_send_ctas = std::max(1, std::min(o->cfg.sms, (o->halo.n + 1023) / 1024));
+    o->n_send_ctas = std::max(1, std::min(o->cfg.sms, (o->halo.n + 255) / 256));   // one vertex per sender thread
     if (const char* w = std::getenv("FEMB_PEER_FUSED_WAVES")) o->fuse_max_waves = std::atoi(w);
-    if (const char* m = std::getenv("FEMB_PEER_MODE")) o->late_send = fused && std::string(m) == "late";
+    if (const char* m = std::getenv("FEMB_PEER_MODE")) {
+      o->late_send = fused && std::string(m) == "late";
+      if (std::string(m) == "one") o->one_kernel = 1;
+      if (std::string(m) == "split") o->one_kernel = 0;
+    }
   }
   FEMB_CUDA(cudaStreamSynchronize(o->stream));
   o->peer = pc;

@@ -31,7 +31,7 @@ constexpr bool kApplyPersist = FEMB_PERSIST_APPLY != 0;   // the operator passes
 
 static int apply_red_slots(const femb_object* o) {
   const bool fused = o->fused_pass(kApplyPersist);   // fused exchange: one CTA per tile (object.h: peer_pass)
-  return apply_tile_grid(o->dtl, o->split_reds(), !fused) + (o->dtl.n_boundary + 255) / 256;
+  return apply_tile_grid(o->dtl, o->split_reds(kApplyPersist), !fused) + (o->dtl.n_boundary + 255) / 256;
 }
 
 static void poll(femb_object* o) {

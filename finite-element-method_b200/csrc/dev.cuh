@@ -63,11 +63,18 @@ struct DevTiling {
   // multi-GPU, set per launch (run_tile_pass) when the halo exchange runs INSIDE the pass's own kernels:
   const HaloDev* hd;     // nullptr: no exchange in this launch
   int n_send;            // tile kernel: its first n_send CTAs send the halo sums of the (finished) halo tiles
+  int send_at;           // -1: the senders are CTAs [0, n_send) of the SECOND launch of a split pass (released by
+                         // griddepcontrol.wait); >= 0: one launch over all tiles, senders are CTAs [send_at, send_at +
+                         // n_send) and wait until the halo tiles -- all of lower CTA index -- have counted themselves done
   int fuse_recv;         // boundary kernel: wait for the neighbours and add their sums itself
   // in-tile completion of boundary vertices (tile_pass.cuh: itc_arrive); nullptr = off (FEMB_ITC=0)
   int32_t* bcount;       // [n_boundary] arrival counters, armed with -(partial slots); shared-with-a-rank: never reached
   const int32_t* halo_b; // [n_halo_b] boundary indices of the vertices shared with another rank
   int n_halo_b;
+  // kernel timeline (femb_trace_enable; diagnostics only): 8 words per launch, set per launch by run_tile_pass --
+  // [0] start of CTA 0, [1] latest CTA end, [2] latest end of a wait for the neighbours, [3] halo flags released,
+  // [4..6] first sender CTA: released / values stored / fence done
+  unsigned long long* trace;
 };
 
 // Shared-memory layout of k_tile (byte offsets; every region is 16-byte aligned):

@@ -19,6 +19,17 @@ void note_launch(const char* what, cudaStream_t) {
   if (err != cudaSuccess) throw std::runtime_error(std::string(what) + ": " + cudaGetErrorString(err));
 }
 
+static int g_trace_next = 0;
+static std::string g_trace_names[kTraceSlots];
+void trace_restart() { g_trace_next = 0; }
+int trace_slots_used() { return g_trace_next; }
+const char* trace_slot_name(int slot) { return slot >= 0 && slot < g_trace_next ? g_trace_names[slot].c_str() : ""; }
+unsigned long long* trace_take_slot(const LaunchCfg& c, const char* name, const char* what) {
+  if (!c.trace || g_trace_next >= kTraceSlots) return nullptr;
+  g_trace_names[g_trace_next] = std::string(name) + ":" + what;
+  return c.trace + kTraceWords * (g_trace_next++);
+}
+
 // ---------------------------------------------------------------------------
 // vertex update shared by the fused step, the stand-alone kinematic kernel
 // ---------------------------------------------------------------------------

@@ -64,6 +64,9 @@ struct LaunchCfg {
   int fuse_recv = 0;             //   phase 2: the boundary kernel receives
   int no_persist = 0;            //   one CTA per tile even for Ops that default to the persistent kernel
   int bnd_send = 0;              //   phase 2 with fuse_recv: sender CTAs at the front of the BOUNDARY kernel ("late send")
+  int send_at = -1;              //   phase 1, part 0, n_send > 0: ONE tile kernel over all tiles whose CTAs
+                                 //   [send_at, send_at + n_send) are the senders; they wait for the halo-tile counter
+  unsigned long long* trace = nullptr;   // kernel timeline buffer (femb_trace_enable); nullptr = off
 };
 
 struct Halo {                    // vertices shared with a neighbouring rank (slab interface planes)
@@ -81,6 +84,10 @@ struct CommHeader {              // at offset 0 of a comm buffer; written by REM
 };
 struct CommState {               // LOCAL device memory: sequence counters (graph-replayable) and the error flag
   uint32_t send_seq, recv_seq, ar_seq, pack_count, unpack_count, error, pad0, pad1;
+  // "one tile kernel" passes (LaunchCfg::send_at): halo tiles finished since the object was bound, and the number
+  // of such passes completed -- a sender CTA of pass p waits for halo_done >= (p + 1) * n_halo_tiles
+  unsigned long long halo_done;
+  uint32_t count_passes, pad2;
 };
 struct PeerComm {                // kernel argument
   char* self;                    // my comm buffer
@@ -97,6 +104,7 @@ struct HaloDev {                 // device-resident: what a tile / boundary kern
   PeerComm pc;
   int n;                         // halo vertices
   const int32_t* hb;             // [n] boundary index of halo vertex k
+  const int2* hrange;            // [n] local partial slots [x, y) of halo vertex k (the remote slot excluded)
   const int32_t* bhalo;          // [n_boundary] halo index of boundary vertex b, -1: not shared
 };
 size_t comm_layout(int n_halo, size_t* recv_off, size_t* slot_off, size_t* recv_stride);
@@ -116,6 +124,12 @@ void launch_halo_mass(const LaunchCfg& c, const DevTiling& tl, Halo h, float4* p
 void launch_halo_zero_remote(const LaunchCfg& c, const DevTiling& tl, Halo h, float4* partial);
 
 // setup: Dm^-1, volume -> element planes; lumped mass -> pos.w   (object.py:345-362)
+// kernel timeline: every launch of run_tile_pass takes the next 8-word slot of LaunchCfg::trace (dev.cuh)
+constexpr int kTraceSlots = 512, kTraceWords = 8;
+void trace_restart();                                   // slot counter back to 0 (new capture)
+int trace_slots_used();
+const char* trace_slot_name(int slot);
+unsigned long long* trace_take_slot(const LaunchCfg& c, const char* name, const char* what);   // nullptr when off / full
 // inverted elements / NaN energy densities / NaN vertices -> out3[0..2] (device)
 void launch_diagnostics(const LaunchCfg& c, int dim, const DevTiling& tl, Planes e, const float4* pos, const float* phi,
                         unsigned long long* out3);

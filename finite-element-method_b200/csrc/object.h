@@ -83,6 +83,7 @@ struct femb_object {
   int red_slots = 0;
   double* d_U = nullptr;
   unsigned long long* d_diag = nullptr;   // femb_diagnostics counters
+  unsigned long long* d_trace = nullptr;  // femb_trace_enable: kernel timeline words
   femb::SolveScalars* d_sc = nullptr;
   femb::SolveScalars* h_sc = nullptr;  // pinned
   int32_t* d_new_of_old = nullptr;
@@ -158,13 +159,22 @@ struct femb_object {
   // vertices; only CTAs that own a shared vertex wait for the neighbours.  Two kernels per pass, no split, no
   // programmatic dependent launch; the NVLink latency hides behind the boundary kernel's own work.
   bool late_send = false;
+  // "one tile kernel" (default wherever the fused form would be chosen; FEMB_PEER_MODE=one|split overrides): halo
+  // tiles first, the sender CTAs in the middle of the SAME launch (they wait for a counter of finished halo tiles),
+  // then the boundary kernel that receives.  Two kernels per pass like on one GPU: the kernel timeline of the N = 8
+  // run (profiles/r02_multi_gpu.txt) shows the split form paying ~12 us per pass for the second ramp-up / tail on a
+  // 2 960-tile slab (halo tiles 22.6 us + other tiles 26.4 us, 5 us overlapped, against 35.2 us for the same
+  // tiles in one launch on one GPU).
+  int one_kernel = -1;              // -1: automatic
+  bool one_pass(bool persistent_op) const { return one_kernel != 0 && fused_pass(persistent_op); }
   bool fused_pass(bool persistent_op) const {
     if (late_send) return false;
     if (!pass_split() || !d_halo_dev) return false;
     return !persistent_op || (dtl.n_tiles - dtl.n_halo_tiles) <= (long long)fuse_max_waves * dtl.grid;
   }
   bool late_pass() const { return late_send && peer_on && d_halo_dev; }
-  bool split_reds() const { return pass_split() && !late_pass(); }   // tile partials laid out as two launches
+  // tile partials laid out as two launches?
+  bool split_reds(bool persistent_op = false) const { return pass_split() && !late_pass() && !one_pass(persistent_op); }
   // One tile pass of a slab rank over peer memory.  f(cfg) launches the pass's kernels for the phase / part
   // in cfg.
   //   fused:   halo tiles | [sender CTAs + other tiles] (programmatic dependent launch) | boundary kernel that
@@ -182,6 +192,17 @@ struct femb_object {
       c2.hd = d_halo_dev;
       c2.fuse_recv = 1;
       c2.bnd_send = n_send_ctas;
+      f(c2);
+      return;
+    }
+    if (one_pass(persistent_op)) {
+      c1.no_persist = c2.no_persist = 1;
+      c1.hd = d_halo_dev;
+      c1.n_send = n_send_ctas;
+      c1.send_at = dtl.n_halo_tiles + cfg.sms * femb::kMinCtas;   // one wave of ordinary tiles after the last halo tile
+      f(c1);
+      c2.hd = d_halo_dev;
+      c2.fuse_recv = 1;
       f(c2);
       return;
     }

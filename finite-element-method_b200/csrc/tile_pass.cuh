@@ -21,6 +21,7 @@
 #include "launch.h"
 #include "tma.cuh"
 
+#include <algorithm>
 #include <stdexcept>
 #include <string>
 #include <type_traits>
@@ -51,6 +52,18 @@ __device__ __forceinline__ void grid_dependency_wait() {
 #if FEMB_PDL
   asm volatile("griddepcontrol.wait;" ::: "memory");
 #endif
+}
+
+// kernel timeline (DevTiling::trace): the last launch's values survive (plain store of CTA 0's start, monotonic
+// maxima for the ends), so after a run of steps the buffer holds the timeline of the final step
+// (launches that exit early -- the solver has converged -- leave the words of the last live launch alone)
+template <class Op>
+__device__ __forceinline__ void trace_start(const DevTiling& tl, const typename Op::Args& a) {
+  if (tl.trace && blockIdx.x == 0 && threadIdx.x == 0 && !Op::early_exit(a)) tl.trace[0] = gtime_ns();
+}
+template <class Op>
+__device__ __forceinline__ void trace_end(const DevTiling& tl, const typename Op::Args& a) {
+  if (tl.trace && threadIdx.x == 0 && !Op::early_exit(a)) atomicMax(tl.trace + 1, gtime_ns());
 }
 
 __device__ __forceinline__ float warp_sum(float v) {
@@ -293,10 +306,12 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile_persistent(Dev
   __shared__ uint64_t s_bar[3];          // [0],[1]: descriptor + local-vertex table buffers; [2]: JDS lists
   __shared__ __align__(16) DevTile s_td[2];
   grid_launch_dependents();
+  trace_start<Op>(tl, a);
   const int n_send = tl.n_send;
   if ((int)blockIdx.x < n_send) {   // sender CTA of a split multi-GPU pass (see run_tile_pass)
     grid_dependency_wait_always();  // the halo tiles (the kernel this one overlaps) are complete and visible
-    halo_send_cta(tl.hd->pc, tl.hd->n, tl.hd->hb, tl.bptr, Op::partial_buf(a), blockIdx.x, n_send);
+    halo_send_cta(tl.hd->pc, tl.hd->n, tl.hd->hrange, Op::partial_buf(a), blockIdx.x, n_send, tl.trace);
+    trace_end<Op>(tl, a);
     return;
   }
   if (Op::early_exit(a)) return;
@@ -434,6 +449,7 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile_persistent(Dev
     const float r = block_sum(red, s_warp);
     if (tid == 0) Op::red_buf(a)[red_off + bid] = (double)r;
   }
+  trace_end<Op>(tl, a);
   grid_dependency_wait_always();
 }
 
@@ -445,16 +461,26 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile(DevTiling tl, 
   __shared__ float s_warp[32];
   __shared__ uint64_t s_bar[2];   // [0]: local-vertex table landed, [1]: JDS lists landed
   grid_launch_dependents();
-  const int n_send = tl.n_send;
-  if ((int)blockIdx.x < n_send) {   // sender CTA of a split multi-GPU pass (see run_tile_pass)
-    grid_dependency_wait_always();  // the halo tiles (the kernel this one overlaps) are complete and visible
-    halo_send_cta(tl.hd->pc, tl.hd->n, tl.hd->hb, tl.bptr, Op::partial_buf(a), blockIdx.x, n_send);
+  trace_start<Op>(tl, a);
+  const int n_send = tl.n_send, send_at = tl.send_at;
+  const int bx = (int)blockIdx.x;
+  const bool counted = send_at >= 0 && n_send > 0;   // one launch over all tiles, senders in the middle of the grid
+  if (n_send > 0 && (counted ? (bx >= send_at && bx < send_at + n_send) : bx < n_send)) {
+    // sender CTA of a multi-GPU pass (see run_tile_pass): the halo tiles are complete and visible
+    if (counted) halo_tiles_wait(tl.hd->pc, tl.n_halo_tiles);
+    else grid_dependency_wait_always();            // (they were the kernel this one overlaps)
+    halo_send_cta(tl.hd->pc, tl.hd->n, tl.hd->hrange, Op::partial_buf(a), counted ? bx - send_at : bx, n_send,
+                  tl.trace, counted);
+    trace_end<Op>(tl, a);
     return;
   }
-  if (Op::early_exit(a)) return;
-  const bool itc = tl.bcount != nullptr && Op::itc(a);
-  const int bid = (int)blockIdx.x - n_send;
+  const int bid = bx - ((counted ? bx >= send_at : true) ? n_send : 0);
   const int tile = t_begin + bid;
+  if (Op::early_exit(a)) {
+    if (counted && tile < tl.n_halo_tiles) halo_tile_done(tl.hd->pc);   // the senders still run: every rank keeps counting
+    return;
+  }
+  const bool itc = tl.bcount != nullptr && Op::itc(a);
   const DevTile td = tl.tiles[tile];
   constexpr int S = kStride;
   const TileSmem lay = tile_smem_layout(tl.max_lv, tl.max_rounds, tl.nc, n_planes<D, Op>());
@@ -521,10 +547,13 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile(DevTiling tl, 
       if (itc) itc_arrive<D, Op>(tl, a, v.gid, sv[l], red);
     }
   }
+  // (recomputed from the launch parameters: nothing extra stays live across the tile)
+  if (tl.send_at >= 0 && tl.n_send > 0 && (int)blockIdx.x < tl.n_halo_tiles) halo_tile_done(tl.hd->pc);
   if (Op::REDUCE) {
     const float r = block_sum(red, s_warp);
     if (threadIdx.x == 0) Op::red_buf(a)[red_off + bid] = (double)r;
   }
+  trace_end<Op>(tl, a);
   grid_dependency_wait_always();
 }
 
@@ -543,9 +572,11 @@ __global__ void __launch_bounds__(kBoundaryBlock) k_boundary(DevTiling tl, typen
   // vertices' local sums into the neighbours' memory (the tile kernel is complete: stream order); the flags travel
   // while the other CTAs finish the ordinary boundary vertices, and only CTAs that own a shared vertex wait for them
   const int n_send = FUSE ? tl.n_send : 0;
+  trace_start<Op>(tl, a);
   if ((int)blockIdx.x < n_send) {
     // (also when the solver has converged: the sequence numbers must keep advancing on every rank)
-    halo_send_cta(hd->pc, hd->n, hd->hb, tl.bptr, Op::partial_buf(a), blockIdx.x, n_send);
+    halo_send_cta(hd->pc, hd->n, hd->hrange, Op::partial_buf(a), blockIdx.x, n_send, tl.trace);
+    trace_end<Op>(tl, a);
     return;
   }
   const unsigned n_recv_ctas = gridDim.x - (unsigned)n_send;
@@ -555,7 +586,7 @@ __global__ void __launch_bounds__(kBoundaryBlock) k_boundary(DevTiling tl, typen
   const int bid = (int)blockIdx.x - n_send;
   const int idx = bid * blockDim.x + threadIdx.x;
   const int b = list ? (idx < n_list ? list[idx] : tl.n_boundary) : idx;
-  if (hd) rparity = halo_recv_begin(hd->pc, rseq, b < tl.n_boundary && hd->bhalo[b] >= 0);
+  if (hd) rparity = halo_recv_begin(hd->pc, rseq, b < tl.n_boundary && hd->bhalo[b] >= 0, tl.trace);
   if (Op::early_exit(a)) {
     if (hd) halo_recv_end(hd->pc, rseq, n_recv_ctas);
     return;
@@ -603,6 +634,7 @@ __global__ void __launch_bounds__(kBoundaryBlock) k_boundary(DevTiling tl, typen
     if (threadIdx.x == 0) Op::red_buf(a)[red_base + bid] = (double)r;
   }
   if (hd) halo_recv_end(hd->pc, rseq, n_recv_ctas);
+  trace_end<Op>(tl, a);
 }
 
 // prefetch helper shared by the Ops: `bytes` per plane starting at slot `slot`
@@ -630,7 +662,9 @@ inline void run_tile_pass(const char* name, const LaunchCfg& c, const DevTiling&
   DevTiling tl = tl_in;          // per-launch copy: the fused halo exchange is switched on per kernel
   tl.hd = c.hd;
   tl.n_send = 0;
+  tl.send_at = -1;
   tl.fuse_recv = 0;
+  tl.trace = nullptr;
   // bytes of dynamic shared memory allowed so far, per kernel function (persistent / one CTA per tile) and per
   // device (the attribute lives in the device's context)
   static int attr_set_all[2][64] = {};
@@ -660,6 +694,7 @@ inline void run_tile_pass(const char* name, const LaunchCfg& c, const DevTiling&
       // With c.n_send, the first n_send CTAs are SENDERS: they wait for the first part (griddepcontrol.wait)
       // and store the halo sums into the neighbours' memory -- no send kernel, no second stream.
       tl.n_send = c.hd ? c.n_send : 0;
+      tl.trace = trace_take_slot(c, name, tl.n_send ? "tiles:rest+send" : "tiles:rest");
       cudaLaunchConfig_t lc = {};
       lc.gridDim = dim3((unsigned)(tile_ctas<Op>(tl, t1 - t0, persist) + tl.n_send));
       lc.blockDim = dim3(Op::BLOCK);
@@ -674,8 +709,19 @@ inline void run_tile_pass(const char* name, const LaunchCfg& c, const DevTiling&
       note_launch(name, c.stream);
       tl.n_send = 0;
     } else if (t1 > t0) {
-      kern<<<tile_ctas<Op>(tl, t1 - t0, persist), Op::BLOCK, smem, c.stream>>>(tl, a, t0, t1, red_off);
+      // c.send_at >= 0 (multi-GPU, all tiles in ONE launch of the one-CTA-per-tile kernel): the halo tiles come
+      // first in tile order; the sender CTAs sit one wave of ordinary tiles behind them, so that by the time they
+      // get their SM slots the halo tiles have (all but) finished and the rest of the kernel hides the transfer
+      const bool one = c.part == 0 && c.hd && c.n_send > 0 && c.send_at >= 0 && !persist;
+      if (one) {
+        tl.n_send = c.n_send;
+        tl.send_at = std::min(c.send_at, t1 - t0);
+      }
+      tl.trace = trace_take_slot(c, name, c.part == 1 ? "tiles:halo" : (one ? "tiles+send" : "tiles"));
+      kern<<<tile_ctas<Op>(tl, t1 - t0, persist) + tl.n_send, Op::BLOCK, smem, c.stream>>>(tl, a, t0, t1, red_off);
       note_launch(name, c.stream);
+      tl.n_send = 0;
+      tl.send_at = -1;
     }
   }
   if (c.ev_mid) cudaEventRecord(c.ev_mid, c.stream);
@@ -687,6 +733,7 @@ inline void run_tile_pass(const char* name, const LaunchCfg& c, const DevTiling&
     tl.fuse_recv = c.hd ? c.fuse_recv : 0;
     tl.n_send = (c.hd && c.fuse_recv) ? c.bnd_send : 0;     // late send: sender CTAs at the front of the boundary kernel
     const int nb = (n_bnd + kBoundaryBlock - 1) / kBoundaryBlock + tl.n_send;
+    tl.trace = trace_take_slot(c, name, tl.n_send ? "boundary+send" : "boundary");
 #if FEMB_PDL
     // programmatic dependent launch: the boundary kernel's CTAs are scheduled while the tile kernel drains
     cudaLaunchConfig_t lc = {};

@@ -30,7 +30,7 @@ EXPORTS = [
     "femb_implicit_solve_finish",
     "femb_advect_implicit", "femb_implicit_assemble", "femb_implicit_apply", "femb_implicit_apply_timed", "femb_render", "femb_get", "femb_set",
     "femb_set_async", "femb_get_async", "femb_transfers_wait", "femb_set_host_threads",
-    "femb_get_energy", "femb_diagnostics", "femb_sync", "femb_last_error", "femb_launch_count", "femb_version",
+    "femb_get_energy", "femb_diagnostics", "femb_trace_enable", "femb_trace_get", "femb_sync", "femb_last_error", "femb_launch_count", "femb_version",
     "femb_tiling_build", "femb_tiling_build_ex", "femb_tiling_destroy", "femb_tiling_info", "femb_tiling_get",
 ]
 
@@ -123,6 +123,8 @@ def lib():
         "femb_set_host_threads": (C.c_int, [i32]),
         "femb_get_energy": (C.c_int, [vp, fp]),
         "femb_diagnostics": (C.c_int, [vp, C.POINTER(C.c_int64)]),
+        "femb_trace_enable": (C.c_int, [vp, C.c_int32]),
+        "femb_trace_get": (C.c_int, [vp, C.POINTER(C.c_uint64), C.c_int32, C.POINTER(C.c_int32), C.c_char_p, C.c_size_t]),
         "femb_sync": (C.c_int, [vp]),
         "femb_last_error": (C.c_char_p, []),
         "femb_launch_count": (C.c_uint64, []),
@@ -273,6 +275,19 @@ class Handle:
         out = (C.c_int64 * 3)()
         check(lib().femb_diagnostics(self._h, out))
         return {"inverted_elements": int(out[0]), "nan_elements": int(out[1]), "nan_vertices": int(out[2])}
+
+    def trace_enable(self, on=True):
+        check(lib().femb_trace_enable(self._h, int(bool(on))))
+
+    def trace_get(self, max_slots=512):
+        """[(name, start_ns, end_ns, wait_end_ns, flags_released_ns, sender_go_ns, sender_stored_ns, sender_fenced_ns, 0)]
+        of the traced launches, in launch order (include/femb200.h: femb_trace_enable)."""
+        words = (C.c_uint64 * (8 * max_slots))()
+        n = C.c_int32()
+        names = C.create_string_buffer(64 * max_slots)
+        check(lib().femb_trace_get(self._h, words, max_slots, C.byref(n), names, len(names)))
+        nm = names.value.decode().split("\n")
+        return [(nm[i],) + tuple(int(words[8 * i + j]) for j in range(8)) for i in range(n.value)]
 
     def kinematic(self, dt, g_dir, use_grad):
         g = gvec(g_dir, self.dim)

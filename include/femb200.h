@@ -220,6 +220,17 @@ int femb_set_async(femb_object *obj, int32_t field, const void *host, size_t byt
 int femb_get_async(femb_object *obj, int32_t field, void *host, size_t bytes);
 int femb_transfers_wait(femb_object *obj);
 /* obj.U[None] (object.py:69) */
+/* Kernel timeline of the tile passes (diagnostics; nothing in the reference corresponds).  While enabled, every
+ * tile / boundary kernel launch records, in its own 8-word slot, %globaltimer nanoseconds of: [0] the start of its
+ * CTA 0, [1] its latest CTA end, [2] the latest end of a wait for a neighbouring rank's halo flags, [3] the release
+ * of this rank's halo flags, [4..6] its first sender CTA: released / values stored / fence done (0 where not
+ * applicable; [7] unused).  Slots are handed out in launch order from 0 after each femb_trace_enable (a cached CUDA
+ * graph keeps the slots it was captured with, so replays overwrite them: after a run of steps the buffer holds the
+ * timeline of the last one).  femb_trace_get synchronises and returns the first n slots (8 words each) and their
+ * newline-separated names ("<pass>:<kernel>").  Serves tools/trace_steps.py -> profiles/r02_multi_gpu.txt. */
+int femb_trace_enable(femb_object *obj, int32_t on);
+int femb_trace_get(femb_object *obj, uint64_t *words, int32_t max_slots, int32_t *n_out, char *names, size_t names_bytes);
+
 /* State diagnostics counted on the device (replaces nothing in the reference -- it has no such check; serves
  * main.py --diag-every): out3 = { elements with det F <= 0 or NaN (explicit.py:24-25 takes
  * log(det F) unclamped), elements whose energy density phi is NaN (as of the last femb_energy_grad), vertices with

@@ -161,15 +161,16 @@ def test_implicit_solve_driver_gloo_world2():
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("comm,extra", [
-    ("peer", {}),                                   # exchange fused into the pass's own kernels (default)
+    ("peer", {}),                                   # default: ONE tile kernel per pass, sender CTAs inside it
+    ("peer", {"FEMB_PEER_MODE": "split"}),          # halo tiles | sender CTAs + other tiles | boundary kernel
     ("peer", {"FEMB_PEER_FUSED_WAVES": "0"}),       # thick-slab variant: persistent operator kernels + send kernel
     ("peer", {"FEMB_PEER_FUSED": "0"}),             # separate send / receive / reduce kernels
     ("peer", {"FEMB_PEER_MODE": "late"}),           # one tile kernel; sender CTAs at the front of the boundary kernel
     ("nccl", {}),
 ])
 def test_two_rank_slabs_match_single_gpu(comm, extra):
-    """comm=peer: halo sums / dot products inside the library's kernels over NVLink peer memory (all three
-    kernel arrangements of csrc/object.h: peer_pass); comm=nccl: the same phases driven from Python with
+    """comm=peer: halo sums / dot products inside the library's kernels over NVLink peer memory (every
+    kernel arrangement of csrc/object.h: peer_pass); comm=nccl: the same phases driven from Python with
     torch.distributed P2P + all_reduce."""
     import torch
 
