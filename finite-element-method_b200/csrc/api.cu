@@ -541,6 +541,7 @@ int femb_peer_bind(femb_object* o, const femb_peer_desc* d) {
   comm_layout(o->halo.n, &pc.recv_off, &pc.slot_off, &pc.recv_stride);
   if (d->recv_stride < o->halo.n) throw ArgError("recv_stride must be the value femb_comm_bytes returned for the largest halo");
   pc.recv_stride = (size_t)d->recv_stride;   // common to all ranks: remote addresses are computed with it
+  comm_ll_offsets(pc.recv_off, pc.recv_stride, &pc.ll_slot_off, &pc.ll_off);
   pc.st = o->alloc<CommState>(1);
   if (!o->side) {
     // highest priority: when the halo tiles finish, the (small) send kernel gets SM slots before the
@@ -569,6 +570,7 @@ int femb_peer_bind(femb_object* o, const femb_peer_desc* d) {
     }
     int2* d_hrange = o->alloc<int2>(hrange.size(), false);
     FEMB_CUDA(cudaMemcpyAsync(d_hrange, hrange.data(), hrange.size() * sizeof(int2), cudaMemcpyHostToDevice, o->stream));
+    o->d_hrange = d_hrange;
     HaloDev hd{pc, o->halo.n, o->halo.b, d_hrange, d_bhalo};
     HaloDev* d_hd = o->alloc<HaloDev>(1, false);
     FEMB_CUDA(cudaMemcpyAsync(d_hd, &hd, sizeof(HaloDev), cudaMemcpyHostToDevice, o->stream));

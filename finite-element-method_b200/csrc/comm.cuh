@@ -34,7 +34,42 @@ __device__ __forceinline__ bool spin_until(const uint32_t* flag, uint32_t seq, C
   return true;
 }
 
+// ---- "LL" words: 32 bits of payload + the 32-bit sequence number of the exchange in ONE 64-bit word, written and
+// read with single (single-copy atomic) 64-bit accesses -- a word whose upper half carries the expected sequence
+// number has arrived, whatever the order in which the words travel.  No system-scope fence, no separate flag, no
+// second round trip: the fence of the flag protocol cost 3-10 us per sender CTA while the SMs stream at full rate
+// (profiles/r02_multi_gpu.txt).  Same idea as NCCL's low-latency protocol.
+__device__ __forceinline__ void ll_store(unsigned long long* p, uint32_t data, uint32_t seq) {
+  const unsigned long long v = ((unsigned long long)seq << 32) | (unsigned long long)data;
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ bool ll_try(const unsigned long long* p, uint32_t seq, uint32_t& data) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  data = (uint32_t)v;
+  return (uint32_t)(v >> 32) == seq;
+}
+// wait for n (<= 4) consecutive words; false on time-out (error flag set)
+template <int N>
+__device__ __forceinline__ bool ll_wait(const unsigned long long* p, uint32_t seq, uint32_t (&data)[N], CommState* st) {
+  const long long t0 = clock64();
+  for (;;) {
+    bool ok = true;
+#pragma unroll
+    for (int i = 0; i < N; ++i) ok = ll_try(p + i, seq, data[i]) && ok;
+    if (ok) return true;
+    if (clock64() - t0 > kSpinLimit) {
+      st->error = 1;
+      return false;
+    }
+  }
+}
+
 __device__ __forceinline__ CommHeader* hdr_of(char* base) { return reinterpret_cast<CommHeader*>(base); }
+// LL halo planes: four words per shared vertex (x, y, z, unused), double-buffered by sequence parity
+__device__ __forceinline__ unsigned long long* ll_plane(char* base, const PeerComm& pc, uint32_t parity) {
+  return reinterpret_cast<unsigned long long*>(base + pc.ll_off) + (size_t)parity * pc.recv_stride * 4;
+}
 __device__ __forceinline__ float4* recv_of(char* base, const PeerComm& pc, uint32_t parity) {
   return reinterpret_cast<float4*>(base + pc.recv_off) + (size_t)parity * pc.recv_stride;
 }
@@ -53,8 +88,8 @@ __device__ __forceinline__ void halo_send_cta(const PeerComm& pc, int n, const i
   CommState* st = pc.st;
   if (trace && cta == 0 && threadIdx.x == 0) trace[4] = gtime_ns();
   const uint32_t seq = st->send_seq + 1, parity = seq & 1u;
-  float4* const lplane = pc.left ? recv_of(pc.left, pc, parity) + pc.left_dst_off : nullptr;
-  float4* const rplane = pc.right ? recv_of(pc.right, pc, parity) + pc.right_dst_off : nullptr;
+  unsigned long long* const lplane = pc.left ? ll_plane(pc.left, pc, parity) + (size_t)pc.left_dst_off * 4 : nullptr;
+  unsigned long long* const rplane = pc.right ? ll_plane(pc.right, pc, parity) + (size_t)pc.right_dst_off * 4 : nullptr;
   for (int k = cta * blockDim.x + threadIdx.x; k < n; k += n_ctas * blockDim.x) {
     const int2 r = hrange[k];
     float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -66,25 +101,29 @@ __device__ __forceinline__ void halo_send_cta(const PeerComm& pc, int n, const i
       for (int j = 0; j < 8; ++j)
         if (i0 + j < r.y) { s.x += p[j].x; s.y += p[j].y; s.z += p[j].z; }
     }
-    if (k < pc.n_left) lplane[k] = s;
-    else rplane[k - pc.n_left] = s;
+    unsigned long long* const dst = k < pc.n_left ? lplane + (size_t)k * 4 : rplane + (size_t)(k - pc.n_left) * 4;
+    ll_store(dst + 0, __float_as_uint(s.x), seq);
+    ll_store(dst + 1, __float_as_uint(s.y), seq);
+    ll_store(dst + 2, __float_as_uint(s.z), seq);
   }
   __syncthreads();
-  if (threadIdx.x == 0) {
+  if (threadIdx.x == 0) {   // local bookkeeping only: the words carry their own sequence number
     if (trace && cta == 0) trace[5] = gtime_ns();
-    __threadfence_system();
-    if (trace && cta == 0) trace[6] = gtime_ns();
     const unsigned prev = atomicAdd(&st->pack_count, 1u);
     if (prev == (unsigned)n_ctas - 1) {
       st->pack_count = 0;
       st->send_seq = seq;
       if (count_pass) st->count_passes = st->count_passes + 1;
-      __threadfence_system();
-      if (pc.left) st_release_sys(&hdr_of(pc.left)->halo_flag[1], seq);
-      if (pc.right) st_release_sys(&hdr_of(pc.right)->halo_flag[0], seq);
       if (trace) trace[3] = gtime_ns();
     }
   }
+}
+
+// the received sum of shared vertex hk of exchange `seq` (k_boundary): waits for its three words
+__device__ __forceinline__ float4 ll_recv_vertex(const PeerComm& pc, uint32_t seq, int hk) {
+  uint32_t w[3];
+  ll_wait<3>(ll_plane(pc.self, pc, seq & 1u) + (size_t)hk * 4, seq, w, pc.st);
+  return make_float4(__uint_as_float(w[0]), __uint_as_float(w[1]), __uint_as_float(w[2]), 0.f);
 }
 
 // "One tile kernel" passes: a halo tile's CTA counts itself done once its partial sums are stored (call with the
@@ -119,18 +158,9 @@ __device__ __forceinline__ void halo_tiles_wait(const PeerComm& pc, int n_halo_t
 // finish advances the sequence (end).  Returns the parity of the receive plane to read.
 // `need`: this thread will read a received value.  Only CTAs that own a shared vertex wait for the neighbours'
 // flags -- the (many) CTAs of ordinary boundary vertices never see the NVLink latency.
-__device__ __forceinline__ uint32_t halo_recv_begin(const PeerComm& pc, uint32_t& seq, bool need = true,
-                                                    unsigned long long* trace = nullptr) {
-  CommState* st = pc.st;
-  seq = st->recv_seq + 1;
-  if (__syncthreads_or(need ? 1 : 0)) {
-    if (threadIdx.x == 0) {
-      if (pc.left) spin_until(&hdr_of(pc.self)->halo_flag[0], seq, st);
-      if (pc.right) spin_until(&hdr_of(pc.self)->halo_flag[1], seq, st);
-      if (trace) atomicMax(trace + 2, gtime_ns());
-    }
-    __syncthreads();
-  }
+// (the LL words are waited for vertex by vertex, ll_recv_vertex: nothing to do here but to read the sequence number)
+__device__ __forceinline__ uint32_t halo_recv_begin(const PeerComm& pc, uint32_t& seq) {
+  seq = pc.st->recv_seq + 1;
   return seq & 1u;
 }
 // n_ctas: CTAs of the grid that call this (the boundary kernel's sender CTAs do not)
@@ -146,31 +176,47 @@ __device__ __forceinline__ void halo_recv_end(const PeerComm& pc, uint32_t seq, 
   }
 }
 
-// this rank's partial `v` -> slot[rank] of every rank, then the flag (lanes 0..world-1 of one warp)
-__device__ __forceinline__ void allsum_scatter(const PeerComm& pc, double v, int lane) {
+// All-sum of up to two doubles over all ranks: this rank's values -> slot[rank] of EVERY rank as LL words (four per
+// value pair: lo / hi halves), then every rank sums the slots in rank order (identical bits on all ranks).  Called
+// by one full warp (lanes 0..world-1 talk to rank `lane`); results valid in lane 0.  Always consumes one sequence
+// number.  Slots are double-buffered by sequence parity.
+__device__ __forceinline__ unsigned long long* ll_slot(char* base, const PeerComm& pc, uint32_t parity, int rank) {
+  return reinterpret_cast<unsigned long long*>(base + pc.ll_slot_off) + ((size_t)parity * kMaxRanks + rank) * 4;
+}
+__device__ __forceinline__ void allsum_scatter2(const PeerComm& pc, double v0, double v1, int lane) {
   const uint32_t seq = pc.st->ar_seq + 1, parity = seq & 1u;
   if (lane < pc.world) {
-    double* slot = reinterpret_cast<double*>(pc.all[lane] + pc.slot_off) + parity * kMaxRanks + pc.rank;
-    *slot = v;
-    __threadfence_system();
-    st_release_sys(&hdr_of(pc.all[lane])->ar_flag[pc.rank], seq);
+    unsigned long long* slot = ll_slot(pc.all[lane], pc, parity, pc.rank);
+    const unsigned long long b0 = (unsigned long long)__double_as_longlong(v0), b1 = (unsigned long long)__double_as_longlong(v1);
+    ll_store(slot + 0, (uint32_t)b0, seq);
+    ll_store(slot + 1, (uint32_t)(b0 >> 32), seq);
+    ll_store(slot + 2, (uint32_t)b1, seq);
+    ll_store(slot + 3, (uint32_t)(b1 >> 32), seq);
   }
 }
-
-// wait for every rank's slot and sum them in rank order (identical bits on all ranks).  Called by one full
-// warp; the result is valid in lane 0.  Always consumes one sequence number.
-__device__ __forceinline__ double allsum_gather(const PeerComm& pc, int lane) {
+__device__ __forceinline__ void allsum_gather2(const PeerComm& pc, int lane, double& s0, double& s1) {
   CommState* st = pc.st;
   const uint32_t seq = st->ar_seq + 1, parity = seq & 1u;
-  if (lane < pc.world) spin_until(&hdr_of(pc.self)->ar_flag[lane], seq, st);
-  __syncwarp();
-  double s = 0.0;
-  if (lane == 0) {
-    const double* slot = reinterpret_cast<const double*>(pc.self + pc.slot_off) + parity * kMaxRanks;
-    for (int i = 0; i < pc.world; ++i) s += __ldcv(slot + i);
-    st->ar_seq = seq;
+  double v0 = 0.0, v1 = 0.0;
+  if (lane < pc.world) {
+    uint32_t w[4] = {0u, 0u, 0u, 0u};
+    ll_wait<4>(ll_slot(pc.self, pc, parity, lane), seq, w, st);
+    v0 = __longlong_as_double((long long)(((unsigned long long)w[1] << 32) | w[0]));
+    v1 = __longlong_as_double((long long)(((unsigned long long)w[3] << 32) | w[2]));
   }
-  return s;
+  s0 = 0.0;
+  s1 = 0.0;
+  for (int i = 0; i < pc.world; ++i) {   // rank order, the same on every rank
+    s0 += __shfl_sync(0xffffffffu, v0, i);
+    s1 += __shfl_sync(0xffffffffu, v1, i);
+  }
+  if (lane == 0) st->ar_seq = seq;
+}
+__device__ __forceinline__ void allsum_scatter(const PeerComm& pc, double v, int lane) { allsum_scatter2(pc, v, 0.0, lane); }
+__device__ __forceinline__ double allsum_gather(const PeerComm& pc, int lane) {
+  double s0, s1;
+  allsum_gather2(pc, lane, s0, s1);
+  return s0;
 }
 
 }  // namespace femb

@@ -24,8 +24,14 @@ namespace femb {
 
 // what == 0: send[k] = sum of the local partial slots of halo vertex k (same order as k_boundary)
 // what == 1: send[k] = {lumped mass of vertex k, 0, 0, 0}
+// what == 2: as 0, but as LL words for a pass whose boundary kernel receives itself (comm.cuh: halo_send_cta)
 __global__ void __launch_bounds__(256) k_halo_send(PeerComm pc, int n, const int32_t* hb, const int32_t* bptr,
-                                                   const float4* partial, const float4* pos, int n_interior, int what) {
+                                                   const int2* hrange, const float4* partial, const float4* pos,
+                                                   int n_interior, int what) {
+  if (what == 2) {
+    halo_send_cta(pc, n, hrange, partial, blockIdx.x, gridDim.x);
+    return;
+  }
   CommState* st = pc.st;
   const uint32_t seq = st->send_seq + 1, parity = seq & 1u;
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
@@ -91,9 +97,10 @@ __global__ void __launch_bounds__(256) k_halo_recv(PeerComm pc, int n, const int
 static inline int nblk(int n) { return (n + 255) / 256; }
 
 void launch_halo_send(const LaunchCfg& c, const DevTiling& tl, const PeerComm& pc, Halo h, const float4* partial,
-                      const float4* pos, int what) {
+                      const float4* pos, int what, const int2* hrange) {
   if (h.n == 0) return;
-  k_halo_send<<<nblk(h.n), 256, 0, c.stream>>>(pc, h.n, h.b, tl.bptr, partial, pos, tl.n_interior, what);
+  if (what == 2 && !hrange) throw std::runtime_error("halo_send: LL send without slot ranges");
+  k_halo_send<<<nblk(h.n), 256, 0, c.stream>>>(pc, h.n, h.b, tl.bptr, hrange, partial, pos, tl.n_interior, what);
   note_launch("halo_send", c.stream);
 }
 void launch_halo_recv(const LaunchCfg& c, const DevTiling& tl, const PeerComm& pc, Halo h, float4* partial,
@@ -109,8 +116,17 @@ size_t comm_layout(int n_halo, size_t* recv_off, size_t* slot_off, size_t* recv_
   off = (off + 255) / 256 * 256;
   *recv_off = off;
   *recv_stride = ((size_t)n_halo + 15) / 16 * 16;   // float4 elements per parity
-  off += 2 * *recv_stride * sizeof(float4);
-  return off;
+  size_t ll_slot, ll;
+  comm_ll_offsets(*recv_off, *recv_stride, &ll_slot, &ll);
+  return ll + 2 * *recv_stride * 4 * sizeof(unsigned long long);
+}
+void comm_ll_offsets(size_t recv_off, size_t recv_stride, size_t* ll_slot_off, size_t* ll_off) {
+  size_t off = recv_off + 2 * recv_stride * sizeof(float4);
+  off = (off + 255) / 256 * 256;
+  *ll_slot_off = off;
+  off += 2 * kMaxRanks * 4 * sizeof(unsigned long long);   // [parity][rank][4 words]
+  off = (off + 255) / 256 * 256;
+  *ll_off = off;                                           // [parity][recv_stride][4 words]
 }
 
 }  // namespace femb

@@ -54,6 +54,27 @@ __device__ double final_sum(const double* red, int n) {
 // memory (pc.st != nullptr) -> every rank's already-reduced partial, gathered through the comm buffers.
 // Result valid in thread 0.  In peer mode a sequence number is consumed on every call, `done` or not.
 // n > 0 in peer mode: this kernel also does the local sum and the scatter (no separate reduce kernel).
+// two sums in ONE exchange (single-reduction CG); results valid in thread 0
+__device__ void global_sum2(const double* red_a, int n_a, const double* red_b, int n_b, const PeerComm& pc, double& a,
+                            double& b) {
+  __shared__ double s_ab[2];
+  const double sa = final_sum(red_a, n_a);
+  __syncthreads();                                       // final_sum's shared scratch is reused
+  const double sb = final_sum(red_b, n_b);
+  if (pc.st == nullptr) {
+    a = sa;
+    b = sb;
+    return;
+  }
+  if (threadIdx.x == 0) { s_ab[0] = sa; s_ab[1] = sb; }
+  __syncthreads();
+  a = b = 0.0;
+  if (threadIdx.x < 32) {
+    allsum_scatter2(pc, s_ab[0], s_ab[1], threadIdx.x);
+    allsum_gather2(pc, threadIdx.x, a, b);
+  }
+}
+
 __device__ double global_sum(const double* red, int n, const PeerComm& pc) {
   if (pc.st == nullptr) return final_sum(red, n);
   if (n > 0) {
@@ -122,9 +143,8 @@ __global__ void __launch_bounds__(kFinalThreads) k_cg_scalar(int kind, int n_red
 __global__ void __launch_bounds__(kFinalThreads) k_cgcg_scalar(int n_g, const double* red_g, int n_d, const double* red_d,
                                                               SolveScalars* sc, float tol, int max_iter, PeerComm pc) {
   if (pc.st == nullptr && sc->done) return;
-  const double g = global_sum(red_g, n_g, pc);
-  __syncthreads();                                       // final_sum's shared scratch is reused
-  const double dl = global_sum(red_d, n_d, pc);
+  double g, dl;
+  global_sum2(red_g, n_g, red_d, n_d, pc, g, dl);        // multi-GPU: one all-sum for both
   if (sc->done) return;
   if (threadIdx.x != 0) return;
   sc->delta_old = sc->delta_new;

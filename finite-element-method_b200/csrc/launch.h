@@ -98,6 +98,7 @@ struct PeerComm {                // kernel argument
   int n_left;                    // halo entries [0, n_left) go to / come from the left neighbour
   int left_dst_off, right_dst_off;   // where my planes start in the neighbours' receive arrays
   size_t recv_off, slot_off, recv_stride;
+  size_t ll_slot_off, ll_off;    // LL all-sum slots / LL halo planes (comm.cuh), behind the float4 receive planes
   CommState* st;
 };
 struct HaloDev {                 // device-resident: what a tile / boundary kernel needs to run the exchange itself
@@ -108,9 +109,12 @@ struct HaloDev {                 // device-resident: what a tile / boundary kern
   const int32_t* bhalo;          // [n_boundary] halo index of boundary vertex b, -1: not shared
 };
 size_t comm_layout(int n_halo, size_t* recv_off, size_t* slot_off, size_t* recv_stride);
-// what: 0 partial sums, 1 lumped masses
+// offsets of the LL areas for a given (common) receive stride
+void comm_ll_offsets(size_t recv_off, size_t recv_stride, size_t* ll_slot_off, size_t* ll_off);
+// what: 0 partial sums, 1 lumped masses (flag protocol, received by launch_halo_recv); 2 partial sums as LL words
+// (received by the boundary kernel itself)
 void launch_halo_send(const LaunchCfg& c, const DevTiling& tl, const PeerComm& pc, Halo h, const float4* partial,
-                      const float4* pos, int what);
+                      const float4* pos, int what, const int2* hrange = nullptr);   // what == 2: LL words (needs hrange)
 void launch_halo_recv(const LaunchCfg& c, const DevTiling& tl, const PeerComm& pc, Halo h, float4* partial,
                       float4* pos, int what);
 // local sum of red[0..n_red) -> slot[rank] of every rank; the consuming scalar kernel gathers the slots

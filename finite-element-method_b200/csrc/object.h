@@ -144,6 +144,7 @@ struct femb_object {
     return static_cast<T*>(p);
   }
   const femb::HaloDev* d_halo_dev = nullptr;   // peer mode, fused exchange (default; FEMB_PEER_FUSED=0 disables)
+  const int2* d_hrange = nullptr;   // local partial slots of every shared vertex (sender side)
   int n_send_ctas = 0;
   cudaStream_t side = nullptr;      // peer mode: the halo send runs here, overlapping the non-halo tiles
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
@@ -227,7 +228,7 @@ struct femb_object {
       FEMB_CUDA(cudaStreamWaitEvent(side, ev_fork, 0));
       LaunchCfg cs = cfg;
       cs.stream = side;
-      launch_halo_send(cs, dtl, peer, halo, vs.partial, vs.pos, 0);
+      launch_halo_send(cs, dtl, peer, halo, vs.partial, vs.pos, d_halo_dev ? 2 : 0, d_hrange);
       FEMB_CUDA(cudaEventRecord(ev_join, side));
       c1.part = 2;
       f(c1);
@@ -235,7 +236,7 @@ struct femb_object {
       c2.part = 1;   // tells the boundary kernel where the tile partials of a split pass end
     } else {
       f(c1);
-      launch_halo_send(c1, dtl, peer, halo, vs.partial, vs.pos, 0);
+      launch_halo_send(c1, dtl, peer, halo, vs.partial, vs.pos, d_halo_dev ? 2 : 0, d_hrange);
     }
     if (d_halo_dev) {
       c2.hd = d_halo_dev;

@@ -586,7 +586,7 @@ __global__ void __launch_bounds__(kBoundaryBlock) k_boundary(DevTiling tl, typen
   const int bid = (int)blockIdx.x - n_send;
   const int idx = bid * blockDim.x + threadIdx.x;
   const int b = list ? (idx < n_list ? list[idx] : tl.n_boundary) : idx;
-  if (hd) rparity = halo_recv_begin(hd->pc, rseq, b < tl.n_boundary && hd->bhalo[b] >= 0, tl.trace);
+  if (hd) rparity = halo_recv_begin(hd->pc, rseq);
   if (Op::early_exit(a)) {
     if (hd) halo_recv_end(hd->pc, rseq, n_recv_ctas);
     return;
@@ -621,7 +621,8 @@ __global__ void __launch_bounds__(kBoundaryBlock) k_boundary(DevTiling tl, typen
       }
     }
     if (hk >= 0) {   // local + remote: the same two-term sum on both owners -> identical bits
-      const float4 r = __ldcv(recv_of(hd->pc.self, hd->pc, rparity) + hk);
+      const float4 r = ll_recv_vertex(hd->pc, rseq, hk);   // waits for this vertex's own words only
+      if (tl.trace) atomicMax(tl.trace + 2, gtime_ns());
       acc[0] += r.x;
       acc[1] += r.y;
       if (D == 3) acc[D - 1] += r.z;
