@@ -622,7 +622,10 @@ __global__ void __launch_bounds__(kBoundaryBlock) k_boundary(DevTiling tl, typen
     }
     if (hk >= 0) {   // local + remote: the same two-term sum on both owners -> identical bits
       const float4 r = ll_recv_vertex(hd->pc, rseq, hk);   // waits for this vertex's own words only
-      if (tl.trace) atomicMax(tl.trace + 2, gtime_ns());
+      if (tl.trace) {   // one lane per warp: tens of thousands of atomics on one word would distort the timeline
+        const unsigned m = __activemask();
+        if ((int)(threadIdx.x & 31) == __ffs(m) - 1) atomicMax(tl.trace + 2, gtime_ns());
+      }
       acc[0] += r.x;
       acc[1] += r.y;
       if (D == 3) acc[D - 1] += r.z;

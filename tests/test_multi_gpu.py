@@ -161,8 +161,8 @@ def test_implicit_solve_driver_gloo_world2():
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("comm,extra", [
-    ("peer", {}),                                   # default: ONE tile kernel per pass, sender CTAs inside it
-    ("peer", {"FEMB_PEER_MODE": "split"}),          # halo tiles | sender CTAs + other tiles | boundary kernel
+    ("peer", {}),                                   # default: halo tiles | sender CTAs + other tiles | boundary kernel
+    ("peer", {"FEMB_PEER_MODE": "one"}),            # ONE tile kernel per pass, sender CTAs inside it (halo-tile counter)
     ("peer", {"FEMB_PEER_FUSED_WAVES": "0"}),       # thick-slab variant: persistent operator kernels + send kernel
     ("peer", {"FEMB_PEER_FUSED": "0"}),             # separate send / receive / reduce kernels
     ("peer", {"FEMB_PEER_MODE": "late"}),           # one tile kernel; sender CTAs at the front of the boundary kernel
