@@ -157,9 +157,9 @@ int femb_object_create(const femb_desc* d, femb_object** out) {
     // vertices shared with another rank get a count that is never reached (the halo boundary kernel owns them)
     // Measured (profiles/r02_ab_itc.log): correct, but SLOWER -- C4 explicit 0.274 -> 0.355 ms, C3 22.7 -> 27.1 us: the
     // fence -> atomic -> dependent loads chain sits at the end of every tile CTA's life and idles its SM slot.
-    // Off unless FEMB_ITC=1.
+    // Compiled in only with -DFEMB_ITC_BUILD=1 (dev.cuh), and then off unless FEMB_ITC=1.
     const char* itc_env = std::getenv("FEMB_ITC");
-    if (t.n_boundary > 0 && itc_env && itc_env[0] == '1') {
+    if (kItcBuild && t.n_boundary > 0 && itc_env && itc_env[0] == '1') {
       std::vector<int32_t> cnt((size_t)t.n_boundary);
       for (int b = 0; b < t.n_boundary; ++b) cnt[b] = t.bptr[b] - t.bptr[b + 1];
       for (int32_t b : t.halo_b) cnt[b] = -(1 << 30);

@@ -20,6 +20,15 @@ namespace femb {
 #ifndef FEMB_PERSIST_ASSEMBLE
 #define FEMB_PERSIST_ASSEMBLE 0
 #endif
+// In-tile completion of boundary vertices (tile_pass.cuh: itc_arrive) is compiled in only on request: measured slower
+// when used (profiles/r02_ab_itc.log), and its mere presence cost the persistent operator kernel 7 % (0.2352 ->
+// 0.2517 ms per pass on C4: register pressure, a 32-byte spill) and the explicit kernel 1.6 %, found by a same-box
+// A/B against the build before it (profiles/r02_ab_old.log).  make EXTRA=-DFEMB_ITC_BUILD=1, then FEMB_ITC=1.
+#ifndef FEMB_ITC_BUILD
+#define FEMB_ITC_BUILD 0
+#endif
+constexpr bool kItcBuild = FEMB_ITC_BUILD != 0;
+
 // Two elements per thread in packed fp32 (FFMA2) for the explicit element kernels, 128-thread CTAs, element planes
 // read from a pair-interleaved copy.  Measured on C4 (B200, same box): 25 % fewer warp instructions (129.5 M vs
 // 173.1 M), issue utilisation 45 % vs 61 %, but half the warps per SM -- 0.2807 ms per step against 0.2752 for the

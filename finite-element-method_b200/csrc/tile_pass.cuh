@@ -315,7 +315,7 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile_persistent(Dev
     return;
   }
   if (Op::early_exit(a)) return;
-  const bool itc = tl.bcount != nullptr && Op::itc(a);
+  const bool itc = kItcBuild && tl.bcount != nullptr && Op::itc(a);
   const int bid = (int)blockIdx.x - n_send;
   int t = t_begin + bid;
   if (t >= t_end) return;
@@ -480,7 +480,7 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile(DevTiling tl, 
     if (counted && tile < tl.n_halo_tiles) halo_tile_done(tl.hd->pc);   // the senders still run: every rank keeps counting
     return;
   }
-  const bool itc = tl.bcount != nullptr && Op::itc(a);
+  const bool itc = kItcBuild && tl.bcount != nullptr && Op::itc(a);
   const DevTile td = tl.tiles[tile];
   constexpr int S = kStride;
   const TileSmem lay = tile_smem_layout(tl.max_lv, tl.max_rounds, tl.nc, n_planes<D, Op>());
@@ -729,7 +729,7 @@ inline void run_tile_pass(const char* name, const LaunchCfg& c, const DevTiling&
     }
   }
   if (c.ev_mid) cudaEventRecord(c.ev_mid, c.stream);
-  const bool itc = tl.bcount != nullptr && Op::itc(a);
+  const bool itc = kItcBuild && tl.bcount != nullptr && Op::itc(a);
   const int32_t* list = itc ? tl.halo_b : nullptr;
   const int n_list = itc ? tl.n_halo_b : 0;
   const int n_bnd = itc ? n_list : tl.n_boundary;
