@@ -356,6 +356,9 @@ int femb_render(femb_object* o, const femb_view* v, const int32_t* prims, int32_
 int femb_trace_enable(femb_object* o, int32_t on) {
   FEMB_TRY
   if (!o) throw ArgError("NULL object");
+  if (on && !kDiagBuild)
+    throw StateError("femb_trace_enable: this build carries no timeline code; load the diagnostics build "
+                     "(make -C csrc diag -> femb200/libfemb200_diag.so, FEMB200_LIB=<path>)");
   FEMB_CUDA(cudaSetDevice(o->device));
   FEMB_CUDA(cudaStreamSynchronize(o->stream));
   // cached graphs carry the trace pointers of the launches they were captured from
@@ -580,7 +583,10 @@ int femb_peer_bind(femb_object* o, const femb_peer_desc* d) {
     if (const char* w = std::getenv("FEMB_PEER_FUSED_WAVES")) o->fuse_max_waves = std::atoi(w);
     if (const char* m = std::getenv("FEMB_PEER_MODE")) {
       o->late_send = fused && std::string(m) == "late";
-      if (std::string(m) == "one") o->one_kernel = 1;
+      if (std::string(m) == "one") {
+        if (!kDiagBuild) throw StateError("FEMB_PEER_MODE=one needs the diagnostics build (libfemb200_diag.so)");
+        o->one_kernel = 1;
+      }
       if (std::string(m) == "split") o->one_kernel = 0;
     }
   }

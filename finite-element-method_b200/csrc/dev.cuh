@@ -20,6 +20,15 @@ namespace femb {
 #ifndef FEMB_PERSIST_ASSEMBLE
 #define FEMB_PERSIST_ASSEMBLE 0
 #endif
+// The diagnostics build (make diag -> femb200/libfemb200_diag.so, FEMB200_LIB selects it) adds the kernel timeline
+// (femb_trace_enable, tools/trace_steps.py) and the "one tile kernel" exchange form (FEMB_PEER_MODE=one).  Their
+// checks cost the explicit tile kernel ~35 instructions per CTA-thread: 1.4 % in a same-box A/B (0.2579 vs 0.2540 ms,
+// profiles/r02_ab_old.log), so the default build carries neither.
+#ifndef FEMB_DIAG_BUILD
+#define FEMB_DIAG_BUILD 0
+#endif
+constexpr bool kDiagBuild = FEMB_DIAG_BUILD != 0;
+
 // In-tile completion of boundary vertices (tile_pass.cuh: itc_arrive) is compiled in only on request: measured slower
 // when used (profiles/r02_ab_itc.log), and its mere presence cost the persistent operator kernel 7 % (0.2352 ->
 // 0.2517 ms per pass on C4: register pressure, a 32-byte spill) and the explicit kernel 1.6 %, found by a same-box

@@ -59,11 +59,11 @@ __device__ __forceinline__ void grid_dependency_wait() {
 // (launches that exit early -- the solver has converged -- leave the words of the last live launch alone)
 template <class Op>
 __device__ __forceinline__ void trace_start(const DevTiling& tl, const typename Op::Args& a) {
-  if (tl.trace && blockIdx.x == 0 && threadIdx.x == 0 && !Op::early_exit(a)) tl.trace[0] = gtime_ns();
+  if (kDiagBuild && tl.trace && blockIdx.x == 0 && threadIdx.x == 0 && !Op::early_exit(a)) tl.trace[0] = gtime_ns();
 }
 template <class Op>
 __device__ __forceinline__ void trace_end(const DevTiling& tl, const typename Op::Args& a) {
-  if (tl.trace && threadIdx.x == 0 && !Op::early_exit(a)) atomicMax(tl.trace + 1, gtime_ns());
+  if (kDiagBuild && tl.trace && threadIdx.x == 0 && !Op::early_exit(a)) atomicMax(tl.trace + 1, gtime_ns());
 }
 
 __device__ __forceinline__ float warp_sum(float v) {
@@ -464,7 +464,8 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile(DevTiling tl, 
   trace_start<Op>(tl, a);
   const int n_send = tl.n_send, send_at = tl.send_at;
   const int bx = (int)blockIdx.x;
-  const bool counted = send_at >= 0 && n_send > 0;   // one launch over all tiles, senders in the middle of the grid
+  // one launch over all tiles, senders in the middle of the grid (diagnostics build only, dev.cuh)
+  const bool counted = kDiagBuild && send_at >= 0 && n_send > 0;
   if (n_send > 0 && (counted ? (bx >= send_at && bx < send_at + n_send) : bx < n_send)) {
     // sender CTA of a multi-GPU pass (see run_tile_pass): the halo tiles are complete and visible
     if (counted) halo_tiles_wait(tl.hd->pc, tl.n_halo_tiles);
@@ -548,7 +549,7 @@ __global__ void __launch_bounds__(Op::BLOCK, Op::MIN_CTAS) k_tile(DevTiling tl, 
     }
   }
   // (recomputed from the launch parameters: nothing extra stays live across the tile)
-  if (tl.send_at >= 0 && tl.n_send > 0 && (int)blockIdx.x < tl.n_halo_tiles) halo_tile_done(tl.hd->pc);
+  if (kDiagBuild && tl.send_at >= 0 && tl.n_send > 0 && (int)blockIdx.x < tl.n_halo_tiles) halo_tile_done(tl.hd->pc);
   if (Op::REDUCE) {
     const float r = block_sum(red, s_warp);
     if (threadIdx.x == 0) Op::red_buf(a)[red_off + bid] = (double)r;
@@ -622,7 +623,7 @@ __global__ void __launch_bounds__(kBoundaryBlock) k_boundary(DevTiling tl, typen
     }
     if (hk >= 0) {   // local + remote: the same two-term sum on both owners -> identical bits
       const float4 r = ll_recv_vertex(hd->pc, rseq, hk);   // waits for this vertex's own words only
-      if (tl.trace) {   // one lane per warp: tens of thousands of atomics on one word would distort the timeline
+      if (kDiagBuild && tl.trace) {   // one lane per warp: tens of thousands of atomics on one word would distort the timeline
         const unsigned m = __activemask();
         if ((int)(threadIdx.x & 31) == __ffs(m) - 1) atomicMax(tl.trace + 2, gtime_ns());
       }

@@ -177,6 +177,11 @@ def test_two_rank_slabs_match_single_gpu(comm, extra):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     env = dict(os.environ, FEMB200_COMM=comm, **extra)
+    if extra.get("FEMB_PEER_MODE") == "one":        # lives in the diagnostics build (csrc/dev.cuh: FEMB_DIAG_BUILD)
+        diag = os.path.join(ROOT, "finite-element-method_b200", "femb200", "libfemb200_diag.so")
+        if not os.path.exists(diag):
+            pytest.skip("libfemb200_diag.so not built (make -C finite-element-method_b200/csrc diag)")
+        env["FEMB200_LIB"] = diag
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
                         "--master-addr", "127.0.0.1", "--master-port", "29611",
                         os.path.join(ROOT, "tests", "mp_slab_check.py")], capture_output=True, text=True, timeout=180,

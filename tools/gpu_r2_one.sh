@@ -17,6 +17,6 @@ except Exception as e:
 PY
 }
 EXTRA="" run split FEMB_X=1
-EXTRA="--no-parity" run one FEMB_PEER_MODE=one
+EXTRA="--no-parity" run one FEMB_PEER_MODE=one FEMB200_LIB=$PWD/finite-element-method_b200/femb200/libfemb200_diag.so
 timeout 400 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29743 tools/trace_steps.py --out gpurun_out/trace_split_n$N.txt > gpurun_out/trace_split_n$N.log 2>&1; echo "trace rc=$?"
 FEMB_PEER_MODE=one timeout 400 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29745 tools/trace_steps.py --out gpurun_out/trace_one_n$N.txt > gpurun_out/trace_one_n$N.log 2>&1; echo "trace one rc=$?"

@@ -15,6 +15,8 @@ import types
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "finite-element-method_b200"))
+# the timeline code lives in the diagnostics build of the library (csrc/dev.cuh: FEMB_DIAG_BUILD)
+os.environ.setdefault("FEMB200_LIB", os.path.join(ROOT, "finite-element-method_b200", "femb200", "libfemb200_diag.so"))
 import bench  # noqa: E402
 
 
