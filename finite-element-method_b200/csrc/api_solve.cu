@@ -12,6 +12,7 @@
 #include <cstring>
 
 #include "object.h"
+#include "sweep.h"
 
 using namespace femb;
 
@@ -38,6 +39,33 @@ static void poll(femb_object* o) {
   FEMB_CUDA(cudaMemcpyAsync(o->h_sc, o->d_sc, sizeof(SolveScalars), cudaMemcpyDeviceToHost, o->stream));
   FEMB_CUDA(cudaStreamSynchronize(o->stream));
   o->check_comm_error();
+}
+
+// tables of the reference-order sweep: built from the host copy of the tiling and uploaded on first use
+void femb_object::ensure_sweep() {
+  if (sweep_tab.vptr) return;
+  SweepHost h;
+  const std::string err = build_sweep(til, h);
+  if (!err.empty()) throw LimitError(err);
+  auto up = [&](auto*& dst, const auto& vec) {
+    using T_ = typename std::remove_reference<decltype(vec)>::type::value_type;
+    T_* p = alloc<T_>(vec.size(), false);
+    if (!vec.empty()) FEMB_CUDA(cudaMemcpyAsync(p, vec.data(), vec.size() * sizeof(T_), cudaMemcpyHostToDevice, stream));
+    dst = p;
+  };
+  SweepTables t{};
+  up(t.inc, h.inc);
+  up(t.sv, h.sv);
+  up(t.lptr, h.lptr);
+  up(t.lverts, h.lverts);
+  up(t.vptr, h.vptr);
+  FEMB_CUDA(cudaStreamSynchronize(stream));   // the host vectors go out of scope
+  sweep_gptr = h.gptr;
+  sweep_gmax.assign(h.gptr.size() - 1, 0);
+  for (size_t g = 0; g + 1 < h.gptr.size(); ++g)
+    for (int l = h.gptr[g]; l < h.gptr[g + 1]; ++l) sweep_gmax[g] = std::max(sweep_gmax[g], h.lptr[l + 1] - h.lptr[l]);
+  sweep_levels = h.n_levels;
+  sweep_tab = t;
 }
 
 static void assemble(femb_object* o, float dt, bool with_diag) {
@@ -217,6 +245,24 @@ void build_program(femb_object* o, SolveProgram& P, float dt, int method, int pr
       it.gsum(vred, [=](int n, const double* red, const PeerComm& pc) { launch_cg_beta(o->cfg, n, red, sc, ktol, max_iter, pc); });
       it.add([=] { launch_cg_update_d(o->cfg, nv, iv, sc); });
     }
+  } else if (method == FEMB_METHOD_SWEEP) {
+    // ---- the reference's damped "Jacobi" in its own iterate order: the serial in-place sweep (391-404) run level by
+    // dependency level (kernels_sweep.cu), loop control of 234-261 on the device
+    if (dist)
+      throw StateError("the reference-order sweep (method 2) orders rows by global vertex id and runs on one GPU; "
+                       "use method 0 or 1 on slab-partitioned objects");
+    o->ensure_sweep();
+    pro.pass([o, dim, dt](const LaunchCfg& c) { launch_implicit_diag(dim, c, o->dtl, o->h, o->vs, dt, o->iv); });
+    pro.add([=] { launch_scale_xyz(o->cfg, nv, iv.b, iv.x, 0.5f); });               // x0 = 0.5 b (231-232)
+    it.pass(apply(0, iv.x, iv.q, AP_RESID, iv.b, iv.r, sc), kApplyPersist);         // compute_error (277-286)
+    it.add([=] { launch_sweep_decide(o->cfg, ared, o->d_red, sc, tol, max_iter, fixed); });
+    it.add([=] { launch_sweep_action(o->cfg, nv, iv.x, iv.past_x, sc); });
+    it.add([o, dim, dt, iv, sc] {
+      const SweepVecs a{o->h.p0, o->h.p1, o->h.p2, o->vs.pos, iv.b, iv.diag, iv.past_x, iv.x, dt * dt};
+      for (size_t g = 0; g + 1 < o->sweep_gptr.size(); ++g)
+        launch_sweep_levels(dim, o->cfg, o->sweep_tab, a, o->sweep_gptr[g], o->sweep_gptr[g + 1] - o->sweep_gptr[g],
+                            o->sweep_gmax[g], sc);
+    });
   } else {
     // ---- the reference's damped "Jacobi" (227-262, 391-404) as a true parallel Jacobi
     pro.pass([o, dim, dt](const LaunchCfg& c) { launch_implicit_diag(dim, c, o->dtl, o->h, o->vs, dt, o->iv); });
@@ -247,7 +293,8 @@ int advance(femb_object* o) {
 void check_solve_args(femb_object* o, int method) {
   if (!o) throw ArgError("NULL object");
   if (!o->implicit) throw StateError("object was created without implicit buffers");
-  if (method != 0 && method != 1) throw ArgError("implicit method must be 0 (Jacobi) or 1 (CG)");
+  if (method != FEMB_METHOD_JACOBI && method != FEMB_METHOD_CG && method != FEMB_METHOD_SWEEP)
+    throw ArgError("implicit method must be 0 (Jacobi), 1 (CG) or 2 (reference-order sweep)");
 }
 
 void finish(femb_object* o, int32_t* iters_out, float* resid_out) {

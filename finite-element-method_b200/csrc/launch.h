@@ -193,6 +193,14 @@ void launch_jacobi_finish(const LaunchCfg& c, int n_vert, ImplicitVecs iv, const
 void launch_jacobi_pass(int dim, const LaunchCfg& c, const DevTiling& tl, Planes h, VertexState vs, float dt,
                         ImplicitVecs iv, double* red, const SolveScalars* sc);
 void launch_scalars_reset(const LaunchCfg& c, SolveScalars* sc);
+// reference-order sweep (kernels_sweep.cu, sweep_core.h): loop control, the accept / revert copy, one group of levels
+struct SweepTables;
+struct SweepVecs;
+void launch_sweep_decide(const LaunchCfg& c, int n_red, const double* red, SolveScalars* sc, float tol, int max_iter,
+                         int fixed);
+void launch_sweep_action(const LaunchCfg& c, int n_vert, float4* x, float4* past, const SolveScalars* sc);
+void launch_sweep_levels(int dim, const LaunchCfg& c, const SweepTables& t, const SweepVecs& a, int lvl0, int n_lvl,
+                         int max_level_rows, const SolveScalars* sc);
 
 // misc vector ops
 void launch_copy_xyz(const LaunchCfg& c, int n, const float4* src, float4* dst);           // dst.xyz = src.xyz

@@ -11,6 +11,7 @@
 
 #include "../../include/femb200.h"
 #include "launch.h"
+#include "sweep_core.h"
 #include "tiling.h"
 
 namespace femb {
@@ -247,6 +248,13 @@ struct femb_object {
     }
     f(c2);
   }
+  // reference-order sweep (FEMB_METHOD_SWEEP, kernels_sweep.cu): incidence tables and level schedule, built and
+  // uploaded by the first solve that asks for it (api_solve.cu) -- objects that never do pay nothing
+  femb::SweepTables sweep_tab{};
+  std::vector<int32_t> sweep_gptr;   // launch plan: group g = levels [gptr[g], gptr[g+1])
+  std::vector<int32_t> sweep_gmax;   // rows of the largest level of group g
+  int sweep_levels = 0;
+  void ensure_sweep();
   // a peer wait that timed out leaves CommState.error set: surface it (call after a stream sync)
   void check_comm_error() {
     if (!peer_on) return;

@@ -152,10 +152,18 @@ int femb_peer_mass(femb_object *obj); /* lumped masses of shared vertices, once 
 
 /* ---- implicit path */
 /* implicit_solver_neo_hookean(obj), implicit.py:201-223, matrix-free.
- * method: 0 Jacobi (implicit.py:227-262), 1 CG (implicit.py:311-386);
+ * method: 0 Jacobi (implicit.py:227-262) as a simultaneous weighted Jacobi, 1 CG (implicit.py:311-386),
+ * 2 (FEMB_METHOD_SWEEP) the reference's "Jacobi" in ITS iterate order -- the serial in-place sweep of
+ * implicit.py:391-404 (rows in ascending vertex id, each row sees the rows before it updated), run level by
+ * dependency level so that the result is the serial one; same start vector, stale past_vec_x, accept / revert /
+ * stop rule as method 0; single-GPU objects only;
  * preconditioned: CG on A^T A x = A^T b (implicit.py:289-299).
  * max_iter<=0 / tol<0 select the reference's constants (500 / 1e-5 for CG,
- * 20000 / 1e-5 for Jacobi).  Writes vel = x. */
+ * 20000 / 1e-5 for Jacobi and the sweep).  tol == 0: exactly max_iter iterations (benchmark / test mode).
+ * Writes vel = x. */
+#define FEMB_METHOD_JACOBI 0
+#define FEMB_METHOD_CG 1
+#define FEMB_METHOD_SWEEP 2
 int femb_implicit_solve(femb_object *obj, float dt, int32_t method, int32_t preconditioned,
                         int32_t max_iter, float tol, int32_t *iters_out, float *resid_out);
 /* advect_implicit(obj, circle_blocks), implicit.py:407-437 */
