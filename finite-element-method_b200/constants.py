@@ -14,6 +14,11 @@ vec = None      # callable: vec(x) -> float32 array of length dim   (reference: 
 mat = None      # callable: mat(x) -> float32 [dim, dim]            (reference: ti.types.matrix)
 index = None    # callable: index(x) -> int32 array of length dim+1
 delta_time = None
+# implicit_method 0 only (extension, config key 'jacobi_order' or env FEMB_JACOBI_ORDER):
+#   'simultaneous' (default) -- weighted Jacobi, all rows at once: the fast GPU form, parity at convergence;
+#   'reference'              -- the reference's serial in-place sweep (implicit.py:391-404) iterate for iterate,
+#                               run by dependency levels (femb_implicit_solve method 2); single GPU only
+jacobi_order = 'simultaneous'
 JACOBIN_METHOD = 0
 CONJUGATE_GRADIENT_METHOD = 1
 

@@ -185,6 +185,9 @@ class Object:
 
     def _implicit_solve(self, dt, method, preconditioned, **kw):
         if self._halo is not None:
+            if method == 2:
+                raise RuntimeError("jacobi_order 'reference' (the serial sweep, rows ordered by global vertex id) runs "
+                                   "on one GPU; slab-partitioned objects use the simultaneous Jacobi or CG")
             return self._halo.implicit_solve(self._h, dt, method, preconditioned, **kw)
         return self._h.implicit_solve(dt, method, preconditioned, **kw)
 

@@ -14,6 +14,8 @@ def sys_init(config):
     constants.implicit_method = config.get('implicit_method')
     constants.preconditioned = config.get('preconditioned')
     constants.vec, constants.mat, constants.index = constants._make_types(constants.dim)
+    # extension key (not in the reference's schema): which iterate order implicit_method 0 follows
+    constants.jacobi_order = config.get('jacobi_order', 'simultaneous')
 
 
 def read_config(file_name):

@@ -105,3 +105,37 @@ def test_sys_init_fills_constants_like_the_reference():
     assert constants.implicit_method == constants.CONJUGATE_GRADIENT_METHOD == 1 and constants.JACOBIN_METHOD == 0
     assert constants.vec(2.0).shape == (3,) and constants.mat(0.0).shape == (3, 3) and constants.index(0).shape == (4,)
     assert constants.vec(1.0).dtype == np.float32 and constants.index(0).dtype == np.int32
+
+
+def test_jacobi_order_selects_the_solver_method(monkeypatch):
+    """implicit_method 0 runs the simultaneous Jacobi unless the config (extension key `jacobi_order`) or the
+    environment asks for the reference's serial sweep order (femb_implicit_solve method 2)."""
+    import constants
+    import utils
+    from solver import implicit
+
+    class Obj:
+        def _implicit_solve(self, dt, method, pre):
+            self.call = (dt, method, pre)
+            return 3, 1e-6
+
+    base = {"dim": 2, "delta_time": 5e-4, "g_dir": [0, -1], "implicit_method": 0, "preconditioned": 0}
+    monkeypatch.delenv("FEMB_JACOBI_ORDER", raising=False)
+    for cfg, env, want in [({}, None, 0), ({"jacobi_order": "reference"}, None, 2), ({}, "reference", 2),
+                           ({"jacobi_order": "reference"}, "simultaneous", 0),
+                           ({"implicit_method": 1, "jacobi_order": "reference", "preconditioned": 1}, None, 1)]:
+        utils.sys_init(dict(base, **cfg))
+        if env is None:
+            monkeypatch.delenv("FEMB_JACOBI_ORDER", raising=False)
+        else:
+            monkeypatch.setenv("FEMB_JACOBI_ORDER", env)
+        obj = Obj()
+        implicit.implicit_solver_neo_hookean(obj)
+        assert obj.call == (5e-4, want, 1 if cfg.get("preconditioned") == 1 else 0)
+        assert obj.last_solve == {"iters": 3, "resid": 1e-6}
+    utils.sys_init(dict(base, jacobi_order="gauss"))
+    monkeypatch.delenv("FEMB_JACOBI_ORDER", raising=False)
+    with pytest.raises(ValueError):
+        implicit.implicit_solver_neo_hookean(Obj())
+    utils.sys_init(base)
+    assert constants.jacobi_order == "simultaneous"

@@ -7,7 +7,7 @@ the real tiling and table builders and runs the solve level by level on the host
   iterate for iterate, the sweep must;
 * oracle.jacobi_iter_field iterate by iterate (error after every sweep, iteration count, revert path);
 * the schedule itself: no star edge inside a level, lower-numbered neighbours strictly earlier.
-What this cannot cover -- the kernel launches and the CUDA-graph loop -- is tests/test_gpu_sweep.py."""
+What this cannot cover -- the kernel launches and the CUDA-graph loop -- is tests/test_zz_gpu_sweep.py."""
 import ctypes as C
 import os
 import subprocess
