@@ -72,6 +72,97 @@ struct Rcb {
 
 }  // namespace
 
+// Bank-aware order of a tile's LOCAL VERTICES (default; FEMB_VERTEX_ORDER=id turns it off).  In the element phase the
+// 8 threads of a quarter warp read, corner by corner, the float4 of their element's vertex from the staged vertices
+// sv[local index] with one 128-bit load: threads that read the same vertex share a wavefront, two DIFFERENT vertices
+// whose local indices agree mod 8 conflict (a float4 spans four banks: bank group = index mod 8).  The local order is
+// fixed only up to ties -- valence descending, for the jagged-diagonal lists -- so inside every run of equal valence
+// the vertices are exchanged until the vertices read together differ mod 8: pairwise-swap descent on
+// sum over (quarter warp, corner, residue) of count^2.  Modelled (tools/bank_model.py): 1.39 -> 1.0x wavefronts per
+// quarter-warp load on C4.  ev[i * nc + c]: vertex (index into the tile's sorted-unique list) of corner c of the
+// tile's i-th element; val: valence by the same index; p: local order -> that index, already sorted by valence.
+static void corner_residue_order(int ne, int nc, const std::vector<int32_t>& ev, const std::vector<int32_t>& val,
+                                 std::vector<int32_t>& p) {
+  const int nl = (int)p.size();
+  const int ns = (ne + 7) / 8 * nc;                  // one set per (quarter warp, corner)
+  std::vector<int32_t> mem((size_t)ns * 8, -1);      // distinct vertices of a set
+  std::vector<uint8_t> nmem(ns, 0), cnt((size_t)ns * 8, 0);
+  std::vector<int32_t> sptr(nl + 1, 0), sets;
+  for (int i = 0; i < ne; ++i)
+    for (int c = 0; c < nc; ++c) {
+      const int si = (i / 8) * nc + c, u = ev[(size_t)i * nc + c];
+      int32_t* m = mem.data() + (size_t)si * 8;
+      int k = 0;
+      while (k < nmem[si] && m[k] != u) ++k;
+      if (k == nmem[si]) { m[nmem[si]++] = u; sptr[u + 1]++; }
+    }
+  for (int u = 0; u < nl; ++u) sptr[u + 1] += sptr[u];
+  sets.resize(sptr[nl]);
+  {
+    std::vector<int32_t> cur(sptr.begin(), sptr.end() - 1);
+    for (int si = 0; si < ns; ++si)
+      for (int k = 0; k < nmem[si]; ++k) sets[cur[mem[(size_t)si * 8 + k]]++] = si;
+  }
+  std::vector<int32_t> pos(nl);
+  for (int l = 0; l < nl; ++l) pos[p[l]] = l;
+  for (int si = 0; si < ns; ++si)
+    for (int k = 0; k < nmem[si]; ++k) cnt[(size_t)si * 8 + (pos[mem[(size_t)si * 8 + k]] & 7)]++;
+  auto in_set = [&](int si, int u) {
+    const int32_t* m = mem.data() + (size_t)si * 8;
+    for (int k = 0; k < nmem[si]; ++k)
+      if (m[k] == u) return true;
+    return false;
+  };
+  auto conflicted = [&](int u) {
+    const int r = pos[u] & 7;
+    for (int q = sptr[u]; q < sptr[u + 1]; ++q)
+      if (cnt[(size_t)sets[q] * 8 + r] > 1) return true;
+    return false;
+  };
+  // change of the objective when u leaves residue ru for rv (sets that also hold `other` keep their counts)
+  auto delta = [&](int u, int ru, int rv, int other) {
+    long d = 0;
+    for (int q = sptr[u]; q < sptr[u + 1]; ++q) {
+      const int si = sets[q];
+      if (in_set(si, other)) continue;
+      d += 2 * ((long)cnt[(size_t)si * 8 + rv] - cnt[(size_t)si * 8 + ru]) + 2;
+    }
+    return d;
+  };
+  auto apply = [&](int u, int ru, int rv, int other) {
+    for (int q = sptr[u]; q < sptr[u + 1]; ++q) {
+      const int si = sets[q];
+      if (in_set(si, other)) continue;
+      cnt[(size_t)si * 8 + ru]--;
+      cnt[(size_t)si * 8 + rv]++;
+    }
+  };
+  for (int pass = 0; pass < 4; ++pass) {
+    bool any = false;
+    for (int a = 0; a < nl;) {
+      int b = a;
+      while (b < nl && val[p[b]] == val[p[a]]) ++b;
+      for (int i = a; i < b; ++i) {
+        if (!conflicted(p[i])) continue;
+        for (int j = a; j < b; ++j) {
+          if (((i ^ j) & 7) == 0) continue;
+          const int u = p[i], v = p[j], ri = i & 7, rj = j & 7;
+          if (delta(u, ri, rj, v) + delta(v, rj, ri, u) >= 0) continue;
+          apply(u, ri, rj, v);
+          apply(v, rj, ri, u);
+          std::swap(p[i], p[j]);
+          pos[u] = j;
+          pos[v] = i;
+          any = true;
+          if (!conflicted(p[i])) break;
+        }
+      }
+      a = b;
+    }
+    if (!any) break;
+  }
+}
+
 // Bank-aware SLOT order (default; FEMB_SLOT_ORDER=id turns it off).  The list order below can only choose AMONG the banks a
 // vertex's incident elements happen to have (bank = slot mod 32); this step chooses those banks.  The elements of
 // every 8-slot block -- one quarter warp of the element phase, the unit a 128-bit shared-memory load is served in, so
@@ -341,7 +432,9 @@ std::string build_tiling(int dim, int n_vert, int n_elem, const float* verts,
     tcount[halo_verts[k]].fetch_add(1 << 20, std::memory_order_relaxed);
   }
 
-  // 4. per tile: in-tile valence, local order (valence descending, then old id)
+  // 4. per tile: in-tile valence, local order (valence descending; ties: bank-aware, see corner_residue_order)
+  const char* vo_env = std::getenv("FEMB_VERTEX_ORDER");   // "id": ties by old id (round-1 tables)
+  const bool vertex_order_bank = !(vo_env && std::string(vo_env) == "id");
   std::vector<std::vector<int32_t>> tval(nt);   // valence in local order
   std::vector<std::vector<int32_t>> tperm(nt);  // local order -> position in sorted-unique list
 #pragma omp parallel for schedule(dynamic, 8)
@@ -359,6 +452,15 @@ std::string build_tiling(int dim, int n_vert, int n_elem, const float* verts,
     p.resize(nl);
     std::iota(p.begin(), p.end(), 0);
     std::stable_sort(p.begin(), p.end(), [&](int32_t a, int32_t b) { return val[a] > val[b]; });
+    if (vertex_order_bank) {
+      std::vector<int32_t> ev((size_t)ne * nc);
+      for (int i = 0; i < ne; ++i)
+        for (int c = 0; c < nc; ++c) {
+          const int32_t g = elems[(int64_t)order[tbeg[ti] + i] * nc + c];
+          ev[(size_t)i * nc + c] = (int32_t)(std::lower_bound(v.begin(), v.end(), g) - v.begin());
+        }
+      corner_residue_order(ne, nc, ev, val, p);
+    }
     tval[ti].resize(nl);
     int n_int = 0;
     for (int l = 0; l < nl; ++l) {

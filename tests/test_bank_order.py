@@ -16,7 +16,7 @@ import bank_model  # noqa: E402
 
 def _model(monkeypatch, cells, **env):
     from femb200 import _capi
-    for k in ("FEMB_SLOT_ORDER", "FEMB_LIST_ORDER"):
+    for k in ("FEMB_SLOT_ORDER", "FEMB_LIST_ORDER", "FEMB_VERTEX_ORDER"):
         monkeypatch.delenv(k, raising=False)
     for k, v in env.items():
         monkeypatch.setenv(k, v)
@@ -30,20 +30,29 @@ def _model(monkeypatch, cells, **env):
 
 def test_gather_wavefronts_per_load(monkeypatch):
     cells = (24, 24, 24)
-    old = _model(monkeypatch, cells, FEMB_SLOT_ORDER="id", FEMB_LIST_ORDER="greedy")    # round-1 tables
-    lst = _model(monkeypatch, cells, FEMB_SLOT_ORDER="id")                               # + lists by matching
-    new = _model(monkeypatch, cells)                                                      # default: + slot order
+    r1 = dict(FEMB_SLOT_ORDER="id", FEMB_LIST_ORDER="greedy", FEMB_VERTEX_ORDER="id")
+    old = _model(monkeypatch, cells, **r1)                                                # round-1 tables
+    lst = _model(monkeypatch, cells, FEMB_SLOT_ORDER="id", FEMB_VERTEX_ORDER="id")       # + lists by matching
+    slo = _model(monkeypatch, cells, FEMB_VERTEX_ORDER="id")                              # + slot order
+    new = _model(monkeypatch, cells)                                                      # default: + vertex order
     g = lambda r: r["gather_wavefronts"] / r["gather_loads"]
-    assert old["gather_loads"] == lst["gather_loads"] == new["gather_loads"]
+    c = lambda r: r["corner_wavefronts"] / r["corner_ideal"]
+    assert old["gather_loads"] == lst["gather_loads"] == slo["gather_loads"] == new["gather_loads"]
     assert 1.7 < g(old) < 2.1                      # what ncu measured on these tables: 1.87
-    assert g(lst) < 1.45 and g(new) < 1.25
-    assert g(new) < g(lst) < g(old)
+    assert g(lst) < 1.45 and g(slo) < 1.25 and g(new) < 1.3
+    assert g(slo) < g(lst) < g(old)
     # the slot order only permutes elements inside 8-slot blocks: the vertex reads of the element phase (128-bit
     # loads, served a quarter warp at a time) keep their wavefronts, every element keeps its tile and its warp
-    assert new["corner_wavefronts"] == old["corner_wavefronts"] == lst["corner_wavefronts"]
+    assert slo["corner_wavefronts"] == old["corner_wavefronts"] == lst["corner_wavefronts"]
+    assert np.array_equal(slo["slot_of_elem"] // 8, old["slot_of_elem"] // 8)
     assert np.array_equal(new["slot_of_elem"] // 8, old["slot_of_elem"] // 8)
-    assert not np.array_equal(new["slot_of_elem"], old["slot_of_elem"])
+    assert not np.array_equal(slo["slot_of_elem"], old["slot_of_elem"])
+    # the vertex order (ties of the valence sort) separates the vertices a quarter warp reads together
+    assert c(old) > 1.25 and c(new) < 1.08
+    # nothing but the order inside the tiles changes: same tiles, same sizes, same list lengths
     assert np.array_equal(new["tiles_arr"], old["tiles_arr"])
+    tot = lambda r: (r["gather_wavefronts"] - r["gather_loads"]) + (r["corner_wavefronts"] - r["corner_ideal"])
+    assert tot(new) < 0.3 * tot(old)               # modelled conflict wavefronts: less than a third of round 1's
 
 
 def test_orders_are_deterministic(monkeypatch):
