@@ -59,3 +59,62 @@ def test_orders_are_deterministic(monkeypatch):
     a = _model(monkeypatch, (12, 12, 12))
     b = _model(monkeypatch, (12, 12, 12))
     assert np.array_equal(a["slot_of_elem"], b["slot_of_elem"]) and a["gather_wavefronts"] == b["gather_wavefronts"]
+
+
+def _full_check(verts, el, T):
+    """Every table consistent under the default orders: lidx decodes to the element's vertices for EVERY slot, and
+    the gather through the lists equals the scatter."""
+    from femb200 import _capi
+    from test_tiling import _emulate
+    verts = np.ascontiguousarray(verts, np.float32)
+    el = np.ascontiguousarray(el, np.int32)
+    nc = el.shape[1]
+    t = _capi.HostTiling(verts, el, T)
+    new_of_old, slot = t.array(0), t.array(1)
+    assert np.array_equal(np.sort(new_of_old), np.arange(len(verts))) and len(np.unique(slot)) == len(el)
+    tiles = t.array(2).reshape(-1, 12)
+    lidx, lv = t.array(6).reshape(-1, 2), t.array(3).reshape(-1, 2)
+    elem_of_slot = np.full(slot.max() + 1, -1)
+    elem_of_slot[slot] = np.arange(len(el))
+    for (slot_off, n_elem, lv_off, n_lv, *_r) in tiles:
+        w = lidx[slot_off:slot_off + n_elem]
+        loc = np.stack([w[:, 0] & 0xFFFF, w[:, 0] >> 16, w[:, 1] & 0xFFFF, w[:, 1] >> 16], axis=1)[:, :nc].astype(np.int64)
+        assert loc.max() < n_lv
+        assert np.array_equal(lv[lv_off + loc, 0], new_of_old[el[elem_of_slot[slot_off:slot_off + n_elem]]])
+    rng = np.random.default_rng(1)
+    vals = rng.standard_normal((len(el), nc, 2))
+    want = np.zeros((len(verts), 2))
+    for c in range(nc):
+        np.add.at(want, el[:, c], vals[:, c])
+    assert np.allclose(_emulate(t, nc, vals), want, rtol=1e-12, atol=1e-12)
+    return t
+
+
+@pytest.mark.parametrize("n_fan, T", [(700, 768), (700, 96), (40, 32), (9, 768)])
+def test_fan_of_triangles_one_hub_of_huge_valence(monkeypatch, n_fan, T):
+    """One vertex shared by every element: valence up to 700 in a tile (rounds >> 32 lanes), short last blocks."""
+    for k in ("FEMB_SLOT_ORDER", "FEMB_LIST_ORDER", "FEMB_VERTEX_ORDER"):
+        monkeypatch.delenv(k, raising=False)
+    ang = np.linspace(0.0, 2 * np.pi, n_fan + 1)[:-1]
+    verts = np.concatenate([[[0.0, 0.0]], np.stack([np.cos(ang), np.sin(ang)], axis=1)])
+    i = np.arange(n_fan)
+    el = np.stack([np.zeros(n_fan, int), 1 + i, 1 + (i + 1) % n_fan], axis=1)
+    rng = np.random.default_rng(n_fan)
+    el = np.stack([np.roll(e, rng.integers(3)) for e in el])       # the hub sits at a different corner per element
+    t = _full_check(verts, el, T)
+    assert t.info["max_rounds"] >= min(n_fan, T) - 1 or t.info["n_tiles"] > 1
+
+
+@pytest.mark.parametrize("dim, n_pts, T, seed", [(3, 400, 768, 1), (3, 900, 128, 2), (2, 1500, 256, 3), (2, 60, 32, 4)])
+def test_unstructured_meshes_under_the_default_orders(monkeypatch, dim, n_pts, T, seed):
+    scipy_spatial = pytest.importorskip("scipy.spatial")
+    for k in ("FEMB_SLOT_ORDER", "FEMB_LIST_ORDER", "FEMB_VERTEX_ORDER"):
+        monkeypatch.delenv(k, raising=False)
+    rng = np.random.default_rng(seed)
+    pts = rng.random((n_pts, dim))
+    pts[: n_pts // 10] = 0.5 + 0.02 * rng.standard_normal((n_pts // 10, dim))   # a dense cluster: high valences
+    el = scipy_spatial.Delaunay(pts).simplices.astype(np.int32)
+    used = np.unique(el)
+    remap = np.full(n_pts, -1)
+    remap[used] = np.arange(used.size)
+    _full_check(pts[used], remap[el], T)
