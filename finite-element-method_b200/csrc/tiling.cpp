@@ -107,27 +107,40 @@ static void corner_residue_order(int ne, int nc, const std::vector<int32_t>& ev,
   for (int l = 0; l < nl; ++l) pos[p[l]] = l;
   for (int si = 0; si < ns; ++si)
     for (int k = 0; k < nmem[si]; ++k) cnt[(size_t)si * 8 + (pos[mem[(size_t)si * 8 + k]] & 7)]++;
-  auto in_set = [&](int si, int u) {
-    const int32_t* m = mem.data() + (size_t)si * 8;
-    for (int k = 0; k < nmem[si]; ++k)
-      if (m[k] == u) return true;
-    return false;
-  };
   auto conflicted = [&](int u) {
     const int r = pos[u] & 7;
     for (int q = sptr[u]; q < sptr[u + 1]; ++q)
       if (cnt[(size_t)sets[q] * 8 + r] > 1) return true;
     return false;
   };
-  // change of the objective when u leaves residue ru for rv (sets that also hold `other` keep their counts)
-  auto delta = [&](int u, int ru, int rv, int other) {
-    long d = 0;
-    for (int q = sptr[u]; q < sptr[u + 1]; ++q) {
+  // Exchange of u (residue ru) and v (residue rv): every set that holds exactly one of them moves one count from the
+  // old residue to the new one, d(objective) = 2 (count[new] - count[old]) + 2; sets that hold both keep their counts.
+  std::vector<uint8_t> mark(ns, 0);                  // sets of the current u
+  long du[8];                                        // u alone to residue r, over ALL its sets
+  auto set_u = [&](int u, int ru, bool on) {
+    for (int q = sptr[u]; q < sptr[u + 1]; ++q) mark[sets[q]] = on;
+    if (!on) return;
+    for (int r = 0; r < 8; ++r) {
+      long d = 0;
+      for (int q = sptr[u]; q < sptr[u + 1]; ++q)
+        d += 2 * ((long)cnt[(size_t)sets[q] * 8 + r] - cnt[(size_t)sets[q] * 8 + ru]) + 2;
+      du[r] = d;
+    }
+  };
+  auto delta_pair = [&](int v, int ru, int rv) {     // needs set_u(u, ru, true)
+    long d = du[rv];
+    for (int q = sptr[v]; q < sptr[v + 1]; ++q) {
       const int si = sets[q];
-      if (in_set(si, other)) continue;
-      d += 2 * ((long)cnt[(size_t)si * 8 + rv] - cnt[(size_t)si * 8 + ru]) + 2;
+      if (mark[si]) d -= 2 * ((long)cnt[(size_t)si * 8 + rv] - cnt[(size_t)si * 8 + ru]) + 2;   // shared: u's term out
+      else d += 2 * ((long)cnt[(size_t)si * 8 + ru] - cnt[(size_t)si * 8 + rv]) + 2;
     }
     return d;
+  };
+  auto in_set = [&](int si, int u) {
+    const int32_t* m = mem.data() + (size_t)si * 8;
+    for (int k = 0; k < nmem[si]; ++k)
+      if (m[k] == u) return true;
+    return false;
   };
   auto apply = [&](int u, int ru, int rv, int other) {
     for (int q = sptr[u]; q < sptr[u + 1]; ++q) {
@@ -144,10 +157,12 @@ static void corner_residue_order(int ne, int nc, const std::vector<int32_t>& ev,
       while (b < nl && val[p[b]] == val[p[a]]) ++b;
       for (int i = a; i < b; ++i) {
         if (!conflicted(p[i])) continue;
+        set_u(p[i], i & 7, true);
         for (int j = a; j < b; ++j) {
           if (((i ^ j) & 7) == 0) continue;
           const int u = p[i], v = p[j], ri = i & 7, rj = j & 7;
-          if (delta(u, ri, rj, v) + delta(v, rj, ri, u) >= 0) continue;
+          if (delta_pair(v, ri, rj) >= 0) continue;
+          set_u(u, ri, false);
           apply(u, ri, rj, v);
           apply(v, rj, ri, u);
           std::swap(p[i], p[j]);
@@ -155,7 +170,9 @@ static void corner_residue_order(int ne, int nc, const std::vector<int32_t>& ev,
           pos[v] = i;
           any = true;
           if (!conflicted(p[i])) break;
+          set_u(p[i], i & 7, true);                  // position i now holds v
         }
+        set_u(p[i], i & 7, false);
       }
       a = b;
     }
