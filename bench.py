@@ -546,7 +546,11 @@ def run_ours(args):
                        "dt": w["dt"], "partition": "x-slabs, %d rank(s), cut by object.Object" % world,
                        "comm": None if halo is None else ("peer memory (in-kernel NVLink stores + flags)" if halo.peer
                                                           else "NCCL P2P + all_reduce"), "tile_elems": prob.info["tile_elems"],
-                       "n_tiles_rank0": prob.info["n_tiles"], "cache": "inputs %.0f MB per rank > 126 MB L2" %
+                       "n_tiles_rank0": prob.info["n_tiles"],
+                       "tile_tables": {"list_order": os.environ.get("FEMB_LIST_ORDER", "matching"),
+                                       "slot_order": os.environ.get("FEMB_SLOT_ORDER", "bank"),
+                                       "vertex_order": os.environ.get("FEMB_VERTEX_ORDER", "bank")},
+                       "cache": "inputs %.0f MB per rank > 126 MB L2" %
                        (algorithmic_bytes(kind, prob.ne_local, prob.nv_local) / 1e6),
                        "state_reset_every": RESET_EVERY if kind == "explicit" else None, "state_finite": finite,
                        "solver_iterations_run": iters, "parity": parity},
